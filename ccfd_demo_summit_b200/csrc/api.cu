@@ -1,0 +1,261 @@
+// Scoring entry points and the latency session (host code above the kernels).
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+#include "ccfd_internal.h"
+
+namespace {
+
+constexpr int64_t kHostChunkRows = 1 << 20;  // 120 MB of fp32 rows per staged chunk
+
+int ensure_staging(ccfd_forest* f, int64_t rows) {
+    if (f->stage_rows >= rows) return CCFD_OK;
+    for (int i = 0; i < 2; ++i) {
+        if (f->stage_stream[i]) CCFD_CUDA(cudaStreamSynchronize(f->stage_stream[i]));
+        cudaFree(f->stage_x[i]);
+        cudaFree(f->stage_p[i]);
+        cudaFree(f->stage_d[i]);
+        f->stage_x[i] = nullptr;
+        f->stage_p[i] = nullptr;
+        f->stage_d[i] = nullptr;
+    }
+    f->stage_rows = 0;
+    for (int i = 0; i < 2; ++i) {
+        if (!f->stage_stream[i]) CCFD_CUDA(cudaStreamCreateWithFlags(&f->stage_stream[i], cudaStreamNonBlocking));
+        CCFD_CUDA(cudaMalloc(&f->stage_x[i], sizeof(float) * (size_t)rows * (size_t)f->dev.n_features));
+        CCFD_CUDA(cudaMalloc(&f->stage_p[i], sizeof(double) * 2 * (size_t)rows));
+        CCFD_CUDA(cudaMalloc(&f->stage_d[i], (size_t)rows));
+    }
+    f->stage_rows = rows;
+    return CCFD_OK;
+}
+
+// Enqueue one scoring of device-resident rows on `stream`; SPLIT takes its scratch from the
+// stream-ordered allocator so concurrent callers never share it.
+int enqueue_device(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel, cudaStream_t stream) {
+    if (kernel == CCFD_KERNEL_AUTO) kernel = ccfd_pick_kernel(f, a.n);
+    void* scratch = nullptr;
+    if (kernel == CCFD_KERNEL_SPLIT) CCFD_CUDA(cudaMallocAsync(&scratch, (size_t)ccfd_split_scratch_bytes(f, a.n), stream));
+    int rc = ccfd_launch_score(f, a, kernel, scratch, stream);
+    if (scratch) {
+        cudaError_t e = cudaFreeAsync(scratch, stream);
+        if (rc == CCFD_OK && e != cudaSuccess) return ccfd_cuda_fail(e, "cudaFreeAsync");
+    }
+    return rc;
+}
+
+int score_impl(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint8_t* decision, double threshold, int ge,
+               uint32_t flags, void* stream_) {
+    if (!f) return ccfd_fail(CCFD_EINVAL, "null forest");
+    if (n < 0) return ccfd_fail(CCFD_EINVAL, "n must be >= 0 (got %lld)", (long long)n);
+    if (n == 0) return CCFD_OK;
+    if (!X) return ccfd_fail(CCFD_EINVAL, "X is null");
+    if (!out && !decision) return ccfd_fail(CCFD_EINVAL, "nothing to write: out and decision are both null");
+    if (ld < f->dev.n_features) return ccfd_fail(CCFD_EINVAL, "row stride %lld is smaller than n_features %d", (long long)ld, f->dev.n_features);
+    if (flags & ~(CCFD_DEVICE_PTRS | CCFD_ASYNC | CCFD_KERNEL_MASK)) return ccfd_fail(CCFD_EINVAL, "unknown flag bits 0x%x", flags);
+    if (threshold != threshold) return ccfd_fail(CCFD_EINVAL, "threshold is NaN");
+    const uint32_t kernel = flags & CCFD_KERNEL_MASK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    DeviceGuard guard(f->device);
+
+    if (flags & CCFD_DEVICE_PTRS) {
+        ScoreArgs a{X, n, ld, out, decision, threshold, ge};
+        int rc = enqueue_device(f, a, kernel, stream);
+        if (rc != CCFD_OK) return rc;
+        if (!(flags & CCFD_ASYNC)) CCFD_CUDA(cudaStreamSynchronize(stream));
+        return CCFD_OK;
+    }
+
+    if (flags & CCFD_ASYNC) return ccfd_fail(CCFD_EINVAL, "CCFD_ASYNC needs CCFD_DEVICE_PTRS (host buffers are copied in chunks and the call must wait)");
+    // Host rows: chunks alternate between two streams, so the copy-in of chunk k+1 and the
+    // copy-out of chunk k-1 overlap the scoring of chunk k.  Every kernel produces the same bits,
+    // so results do not depend on how the request is chunked.
+    std::lock_guard<std::mutex> lock(f->host_mu);
+    const int64_t chunk = std::min<int64_t>(n, kHostChunkRows);
+    int rc = ensure_staging(f, chunk);
+    if (rc != CCFD_OK) return rc;
+    const int F = f->dev.n_features;
+    int k = 0;
+    for (int64_t r0 = 0; r0 < n; r0 += chunk, ++k) {
+        const int s = k & 1;
+        const int64_t rows = std::min<int64_t>(chunk, n - r0);
+        cudaStream_t st = f->stage_stream[s];
+        if (ld == F)
+            CCFD_CUDA(cudaMemcpyAsync(f->stage_x[s], X + r0 * ld, sizeof(float) * (size_t)rows * F, cudaMemcpyHostToDevice, st));
+        else
+            CCFD_CUDA(cudaMemcpy2DAsync(f->stage_x[s], sizeof(float) * F, X + r0 * ld, sizeof(float) * (size_t)ld, sizeof(float) * F, (size_t)rows, cudaMemcpyHostToDevice, st));
+        ScoreArgs a{f->stage_x[s], rows, F, out ? f->stage_p[s] : nullptr, decision ? f->stage_d[s] : nullptr, threshold, ge};
+        rc = enqueue_device(f, a, kernel, st);
+        if (rc != CCFD_OK) break;
+        if (out) CCFD_CUDA(cudaMemcpyAsync(out + 2 * r0, f->stage_p[s], sizeof(double) * 2 * (size_t)rows, cudaMemcpyDeviceToHost, st));
+        if (decision) CCFD_CUDA(cudaMemcpyAsync(decision + r0, f->stage_d[s], (size_t)rows, cudaMemcpyDeviceToHost, st));
+    }
+    for (int s = 0; s < 2; ++s) {
+        cudaError_t e = cudaStreamSynchronize(f->stage_stream[s]);
+        if (rc == CCFD_OK && e != cudaSuccess) rc = ccfd_cuda_fail(e, "cudaStreamSynchronize");
+    }
+    return rc;
+}
+
+}  // namespace
+
+extern "C" int ccfd_predict_proba(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint32_t flags, void* stream) {
+    if (!out && n > 0) return ccfd_fail(CCFD_EINVAL, "out is null");
+    return score_impl(f, X, n, ld, out, nullptr, 0.5, 0, flags, stream);
+}
+
+extern "C" int ccfd_predict_decision(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint8_t* decision, double threshold,
+                                     int ge, uint32_t flags, void* stream) {
+    if (!decision && n > 0) return ccfd_fail(CCFD_EINVAL, "decision is null");
+    return score_impl(f, X, n, ld, out, decision, threshold, ge, flags, stream);
+}
+
+// ===================================================================================== session
+struct ccfd_slot {
+    float* hx = nullptr;   // pinned, max_batch * F
+    double* hp = nullptr;  // pinned, max_batch * 2
+    float* dx = nullptr;
+    double* dp = nullptr;
+    void* scratch = nullptr;
+    cudaStream_t stream = nullptr;
+    std::vector<cudaGraphExec_t> exec;  // one per bucket
+    bool busy = false;
+};
+
+struct ccfd_session {
+    ccfd_forest* f = nullptr;
+    int64_t max_batch = 0;
+    std::vector<int64_t> buckets;  // ascending capacities; a request runs the smallest that holds it
+    std::vector<ccfd_slot> slots;
+};
+
+namespace {
+
+void free_slot(ccfd_slot& s) {
+    if (s.stream) cudaStreamSynchronize(s.stream);
+    for (cudaGraphExec_t e : s.exec)
+        if (e) cudaGraphExecDestroy(e);
+    s.exec.clear();
+    cudaFreeHost(s.hx);
+    cudaFreeHost(s.hp);
+    cudaFree(s.dx);
+    cudaFree(s.dp);
+    cudaFree(s.scratch);
+    if (s.stream) cudaStreamDestroy(s.stream);
+    s = ccfd_slot();
+}
+
+int build_slot(ccfd_session* ss, ccfd_slot& s) {
+    const ccfd_forest* f = ss->f;
+    const int F = f->dev.n_features;
+    const size_t xb = sizeof(float) * (size_t)ss->max_batch * F, pb = sizeof(double) * 2 * (size_t)ss->max_batch;
+    CCFD_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    CCFD_CUDA(cudaHostAlloc(&s.hx, xb, cudaHostAllocDefault));
+    CCFD_CUDA(cudaHostAlloc(&s.hp, pb, cudaHostAllocDefault));
+    memset(s.hx, 0, xb);
+    CCFD_CUDA(cudaMalloc(&s.dx, xb));
+    CCFD_CUDA(cudaMalloc(&s.dp, pb));
+    int64_t scratch_bytes = 0;
+    for (int64_t cap : ss->buckets)
+        if (ccfd_pick_kernel(f, cap) == CCFD_KERNEL_SPLIT) scratch_bytes = std::max(scratch_bytes, ccfd_split_scratch_bytes(f, cap));
+    if (scratch_bytes) CCFD_CUDA(cudaMalloc(&s.scratch, (size_t)scratch_bytes));
+
+    // One graph per bucket: copy in -> score -> copy out, all addresses fixed at capture.
+    for (int64_t cap : ss->buckets) {
+        cudaGraph_t graph = nullptr;
+        CCFD_CUDA(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
+        cudaError_t e = cudaMemcpyAsync(s.dx, s.hx, sizeof(float) * (size_t)cap * F, cudaMemcpyHostToDevice, s.stream);
+        int rc = CCFD_OK;
+        if (e == cudaSuccess) {
+            ScoreArgs a{s.dx, cap, F, s.dp, nullptr, 0.5, 0};
+            rc = ccfd_launch_score(f, a, ccfd_pick_kernel(f, cap), s.scratch, s.stream);
+        }
+        if (e == cudaSuccess && rc == CCFD_OK) e = cudaMemcpyAsync(s.hp, s.dp, sizeof(double) * 2 * (size_t)cap, cudaMemcpyDeviceToHost, s.stream);
+        cudaError_t e2 = cudaStreamEndCapture(s.stream, &graph);
+        if (rc != CCFD_OK) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc;
+        }
+        if (e != cudaSuccess) {
+            if (graph) cudaGraphDestroy(graph);
+            return ccfd_cuda_fail(e, "graph capture");
+        }
+        if (e2 != cudaSuccess) return ccfd_cuda_fail(e2, "cudaStreamEndCapture");
+        cudaGraphExec_t exec = nullptr;
+        e = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) return ccfd_cuda_fail(e, "cudaGraphInstantiate");
+        s.exec.push_back(exec);
+        // first launch uploads the graph; do it now so no request pays for it
+        CCFD_CUDA(cudaGraphLaunch(exec, s.stream));
+    }
+    CCFD_CUDA(cudaStreamSynchronize(s.stream));
+    return CCFD_OK;
+}
+
+}  // namespace
+
+extern "C" int ccfd_session_create(ccfd_forest* f, int64_t max_batch, int32_t n_slots, ccfd_session** out) {
+    if (!f || !out) return ccfd_fail(CCFD_EINVAL, "null argument");
+    *out = nullptr;
+    if (max_batch < 1 || max_batch > (1 << 22)) return ccfd_fail(CCFD_EINVAL, "max_batch must be in 1..4194304 (got %lld)", (long long)max_batch);
+    if (n_slots < 1 || n_slots > 64) return ccfd_fail(CCFD_EINVAL, "n_slots must be in 1..64 (got %d)", n_slots);
+    ccfd_session* ss = new (std::nothrow) ccfd_session();
+    if (!ss) return ccfd_fail(CCFD_ENOMEM, "out of host memory");
+    ss->f = f;
+    ss->max_batch = max_batch;
+    for (int64_t cap = 32; cap < max_batch; cap *= 2) ss->buckets.push_back(cap);
+    ss->buckets.push_back(max_batch);
+    DeviceGuard guard(f->device);
+    ss->slots.resize((size_t)n_slots);
+    for (auto& s : ss->slots) {
+        int rc = build_slot(ss, s);
+        if (rc != CCFD_OK) {
+            ccfd_session_destroy(ss);
+            return rc;
+        }
+    }
+    *out = ss;
+    return CCFD_OK;
+}
+
+extern "C" int ccfd_session_destroy(ccfd_session* ss) {
+    if (!ss) return CCFD_OK;
+    DeviceGuard guard(ss->f->device);
+    for (auto& s : ss->slots) free_slot(s);
+    delete ss;
+    return CCFD_OK;
+}
+
+extern "C" int ccfd_session_buffers(ccfd_session* ss, int32_t slot, float** x, double** p) {
+    if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
+    if (slot < 0 || slot >= (int32_t)ss->slots.size()) return ccfd_fail(CCFD_EINVAL, "slot %d out of range", slot);
+    if (x) *x = ss->slots[(size_t)slot].hx;
+    if (p) *p = ss->slots[(size_t)slot].hp;
+    return CCFD_OK;
+}
+
+extern "C" int ccfd_session_submit(ccfd_session* ss, int32_t slot, int64_t n_rows) {
+    if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
+    if (slot < 0 || slot >= (int32_t)ss->slots.size()) return ccfd_fail(CCFD_EINVAL, "slot %d out of range", slot);
+    if (n_rows < 1 || n_rows > ss->max_batch) return ccfd_fail(CCFD_EINVAL, "n_rows must be in 1..%lld (got %lld)", (long long)ss->max_batch, (long long)n_rows);
+    ccfd_slot& s = ss->slots[(size_t)slot];
+    if (s.busy) return ccfd_fail(CCFD_ESTATE, "slot %d is in flight: wait before submitting again", slot);
+    size_t b = 0;
+    while (ss->buckets[b] < n_rows) ++b;
+    DeviceGuard guard(ss->f->device);
+    CCFD_CUDA(cudaGraphLaunch(s.exec[b], s.stream));
+    s.busy = true;
+    return CCFD_OK;
+}
+
+extern "C" int ccfd_session_wait(ccfd_session* ss, int32_t slot) {
+    if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
+    if (slot < 0 || slot >= (int32_t)ss->slots.size()) return ccfd_fail(CCFD_EINVAL, "slot %d out of range", slot);
+    ccfd_slot& s = ss->slots[(size_t)slot];
+    if (!s.busy) return ccfd_fail(CCFD_ESTATE, "slot %d has nothing in flight", slot);
+    s.busy = false;
+    CCFD_CUDA(cudaStreamSynchronize(s.stream));
+    return CCFD_OK;
+}

@@ -1,0 +1,110 @@
+// Internal declarations shared by the library's translation units (not part of the ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "ccfd_rf.h"
+
+// ----------------------------------------------------------------------------------------------
+// Packed node, 8 bytes.  Trees are laid out breadth-first with the two children of a node in
+// adjacent slots, so one child position serves both: next = child + (go_right ? 1 : 0).
+//   internal : thr  = largest fp32 <= sklearn's fp64 threshold      (x <= thr  <=>  go left)
+//              meta = child_pos << 9 | missing_go_to_left << 8 | feature
+//   leaf     : thr  = bit pattern of the tree-local leaf-value index (a non-negative tiny float)
+//              meta = own_pos << 9 | n_features   -> reads the all-zero dummy feature row, 0 <= thr
+//                     always holds, so a leaf steps to itself and fixed-trip loops need no leaf test.
+// Breadth-first order keeps each level contiguous: the top levels (<= 16 nodes = 128 B) are
+// shared-memory bank-conflict free however the 32 rows of a warp spread over them.
+// ----------------------------------------------------------------------------------------------
+struct PackedNode {
+    float thr;
+    uint32_t meta;
+};
+static_assert(sizeof(PackedNode) == 8, "node must be 8 bytes");
+
+constexpr uint32_t kFeatMask = 0xFFu;
+constexpr uint32_t kMglBit = 0x100u;
+constexpr int kChildShift = 9;
+constexpr int64_t kMaxNodesPerTree = (int64_t)1 << 23;
+
+// Per-tree record read by the kernels (16 bytes).
+struct TreeRec {
+    uint32_t blob_off16;   // offset of the tree's blob in the forest buffer, in 16-byte units
+    uint32_t blob_bytes;   // nodes + padding + leaf values, multiple of 16
+    uint32_t values_off;   // byte offset of the leaf values inside the blob (multiple of 16)
+    uint32_t depth;        // longest root-to-leaf path = trip count of the descent loop
+};
+static_assert(sizeof(TreeRec) == 16, "TreeRec must be 16 bytes");
+
+struct ForestDev {
+    const uint8_t* blob;     // all tree blobs back to back, 16-byte aligned each
+    const TreeRec* trees;    // [n_trees]
+    int32_t n_trees;
+    int32_t n_features;
+    uint32_t max_tree_bytes; // largest blob
+    uint32_t max_depth;
+};
+
+struct ccfd_forest {
+    int device = 0;
+    ForestDev dev{};
+    ccfd_forest_info info{};
+    std::vector<TreeRec> host_trees;
+    int sm_count = 0;
+    int smem_optin = 0;
+    // host-pointer path: staging owned by the forest, one host call at a time
+    std::mutex host_mu;
+    float* stage_x[2] = {nullptr, nullptr};
+    double* stage_p[2] = {nullptr, nullptr};
+    uint8_t* stage_d[2] = {nullptr, nullptr};
+    cudaStream_t stage_stream[2] = {nullptr, nullptr};
+    int64_t stage_rows = 0;
+};
+
+// error plumbing -------------------------------------------------------------------------------
+int ccfd_fail(int code, const char* fmt, ...);
+int ccfd_cuda_fail(cudaError_t e, const char* what);
+#define CCFD_CUDA(call)                                              \
+    do {                                                             \
+        cudaError_t _e = (call);                                     \
+        if (_e != cudaSuccess) return ccfd_cuda_fail(_e, #call);     \
+    } while (0)
+
+class DeviceGuard {
+  public:
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev_) != cudaSuccess) prev_ = -1;
+        if (prev_ != dev) cudaSetDevice(dev);
+        dev_ = dev;
+    }
+    ~DeviceGuard() {
+        if (prev_ >= 0 && prev_ != dev_) cudaSetDevice(prev_);
+    }
+
+  private:
+    int prev_ = -1, dev_ = 0;
+};
+
+// kernels.cu -------------------------------------------------------------------------------------
+struct ScoreArgs {
+    const float* X;     // device
+    int64_t n;
+    int64_t ld;
+    double* out;        // device, may be null when only decisions are wanted
+    uint8_t* decision;  // device, may be null
+    double threshold;
+    int ge;
+};
+
+// Pick + launch.  `kernel` is one of CCFD_KERNEL_*; scratch is used by SPLIT only
+// (n * n_trees * 16 bytes) and may be null for the others.
+int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel, void* scratch,
+                      cudaStream_t stream);
+uint32_t ccfd_pick_kernel(const ccfd_forest* f, int64_t n);
+int64_t ccfd_split_scratch_bytes(const ccfd_forest* f, int64_t n);
+int ccfd_kernels_init(ccfd_forest* f);

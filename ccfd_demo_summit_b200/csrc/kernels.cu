@@ -1,0 +1,505 @@
+// sm_100a kernels of the scoring path: forest descent + leaf gather + ordered accumulate + divide,
+// fused.  Replaces Tree._apply_dense (SK/tree/_tree.pyx:954-996), Tree.predict's value.take
+// (SK/tree/_tree.pyx:939-945), _accumulate_prediction (SK/ensemble/_forest.py:704-717) and the
+// final divide (SK/ensemble/_forest.py:961-962).
+//
+// Mapping, common to the three kernels: one lane = one row, so a row's float64 sum runs over
+// trees 0..T-1 in order inside one thread exactly as scikit-learn's n_jobs=1 loop does, and
+// results are bit-identical.  Rows live in shared memory transposed ([feature][row], row stride
+// odd) so that the data-dependent `x[feature]` fetch of 32 lanes always hits 32 different banks.
+//
+//   STREAM  throughput.  A persistent CTA keeps 512*SPT rows resident and streams the whole forest
+//           through a shared-memory ring with 1-D TMA bulk copies (cp.async.bulk + mbarrier
+//           complete_tx), one producer warp feeding 16 consumer warps.
+//   SPLIT   latency.  Grid = row tiles x tree chunks so a 1-1024 row request still covers the
+//           chip; per-(tree,row) leaf values go to scratch and a second kernel adds them in tree
+//           order.
+//   GLOBAL  forests whose trees do not fit a shared-memory stage: nodes come from L2/HBM.
+#include "ccfd_internal.h"
+
+namespace {
+
+constexpr int kConsumerWarps = 16;
+constexpr int kConsumerThreads = kConsumerWarps * 32;
+constexpr int kStreamThreads = kConsumerThreads + 32;  // + one producer warp
+constexpr int kMaxStages = 8;
+constexpr int kTileThreads = 256;                      // SPLIT and GLOBAL: one row per thread
+constexpr int kSplitStages = 2;
+
+__host__ __device__ constexpr uint32_t round_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
+
+// ------------------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra MBAR_DONE;\n"
+        "bra MBAR_WAIT;\n"
+        "MBAR_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D TMA: global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+// barrier + OR-reduction of a predicate over the participating threads
+__device__ __forceinline__ bool named_bar_or(int id, int nthreads, bool pred) {
+    uint32_t r;
+    asm volatile(
+        "{\n"
+        ".reg .pred p, q;\n"
+        "setp.ne.u32 q, %1, 0;\n"
+        "bar.red.or.pred p, %2, %3, q;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(r)
+        : "r"((uint32_t)pred), "r"(id), "r"(nthreads)
+        : "memory");
+    return r != 0;
+}
+// streaming 128-bit load: rows are read once, keep them out of L1
+__device__ __forceinline__ float4 ld_stream4(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+// --------------------------------------------------------------------- row tile -> shared memory
+// Copies `rows` rows starting at src into xs[feature * XS + row] (transposed) with coalesced
+// reads, zero-fills rows [rows, S) so the descent of idle lanes stays on finite values, and
+// reports whether this thread saw a NaN.  XS is odd (== 1 mod 32): the transposed stores of one
+// warp spread over the banks, and the descent's reads (lane == row) are conflict-free.
+template <int NT, int S>
+__device__ __forceinline__ bool load_tile(float* xs, const float* __restrict__ src, int rows, int64_t ld, int F, bool vec_ok, int tid) {
+    constexpr int XS = S + 1;
+    bool nan = false;
+    const int total = rows * F;
+    if (vec_ok) {
+        const float4* src4 = reinterpret_cast<const float4*>(src);
+        const int nvec = total >> 2;
+#pragma unroll 4
+        for (int v = tid; v < nvec; v += NT) {
+            const float4 q = ld_stream4(src4 + v);
+            const int e = v << 2;
+            int r = e / F, c = e - r * F;
+            const float qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                xs[c * XS + r] = qq[j];
+                nan |= (qq[j] != qq[j]);
+                if (++c == F) {
+                    c = 0;
+                    ++r;
+                }
+            }
+        }
+        for (int e = (nvec << 2) + tid; e < total; e += NT) {
+            const int r = e / F, c = e - r * F;
+            const float v = __ldg(src + e);
+            xs[c * XS + r] = v;
+            nan |= (v != v);
+        }
+    } else {
+        for (int e = tid; e < total; e += NT) {
+            const int r = e / F, c = e - r * F;
+            const float v = __ldg(src + (int64_t)r * ld + c);
+            xs[c * XS + r] = v;
+            nan |= (v != v);
+        }
+    }
+    if (rows < S) {
+        const int pad = (S - rows) * F;
+        for (int e = tid; e < pad; e += NT) {
+            const int r = e / F, c = e - r * F;
+            xs[c * XS + rows + r] = 0.0f;
+        }
+    }
+    return nan;
+}
+
+// ------------------------------------------------------------------------------ the descent
+// One step per level, no branch: x <= thr picks the left slot of the sibling pair, anything else
+// (including NaN on the NaN-free path) the right one.  With NAN_AWARE a NaN follows the node's
+// missing_go_to_left bit (SK/tree/_tree.pyx:984-988).  Leaves step to themselves.
+template <bool NAN_AWARE>
+__device__ __forceinline__ uint32_t step(const uint2 nd, const float x) {
+    bool left = x <= __uint_as_float(nd.x);
+    if (NAN_AWARE) left = (x != x) ? ((nd.y & kMglBit) != 0u) : left;
+    return (nd.y >> kChildShift) + (left ? 0u : 1u);
+}
+
+// Nodes in shared memory, SPT independent rows per thread interleaved for ILP.
+template <int SPT, int STRIDE, bool NAN_AWARE>
+__device__ __forceinline__ void descend_smem(const uint2* __restrict__ nodes, const float* __restrict__ xcol, int XS, int depth, uint32_t (&vidx)[SPT]) {
+    uint2 nd[SPT];
+    const uint2 root = nodes[0];
+#pragma unroll
+    for (int i = 0; i < SPT; ++i) nd[i] = root;
+#pragma unroll 2
+    for (int d = 0; d < depth; ++d) {
+#pragma unroll
+        for (int i = 0; i < SPT; ++i) {
+            const float x = xcol[(nd[i].y & kFeatMask) * XS + i * STRIDE];
+            nd[i] = nodes[step<NAN_AWARE>(nd[i], x)];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < SPT; ++i) vidx[i] = nd[i].x;
+}
+
+// =============================================================================== STREAM kernel
+// smem: [0,128) mbarriers | xs (F+1 rows of XS floats, last row = zeros) | ring of tree stages
+template <int SPT>
+__global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const uint32_t stage_bytes, const int vec_ok) {
+    constexpr int S = kConsumerThreads * SPT;
+    constexpr int XS = S + 1;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+    uint64_t* empty = full + kMaxStages;
+    float* xs = reinterpret_cast<float*>(smem + 128);
+    const int F = f.n_features;
+    const int T = f.n_trees;
+    uint8_t* ring = smem + 128 + round_up((uint32_t)(F + 1) * XS * 4u, 128u);
+    const int tid = threadIdx.x;
+    const int64_t n_batches = (a.n + S - 1) / S;
+
+    if (tid == 0) {
+        for (int s = 0; s < n_stages; ++s) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, kConsumerWarps);
+        }
+        mbar_fence_init();
+    }
+    for (int i = tid; i < XS; i += kStreamThreads) xs[F * XS + i] = 0.0f;
+    __syncthreads();
+
+    if (tid >= kConsumerThreads) {
+        // ---- producer warp: one lane streams tree blobs, forest after forest, batch after batch
+        if (tid == kConsumerThreads) {
+            int64_t my_batches = 0;
+            if ((int64_t)blockIdx.x < n_batches) my_batches = (n_batches - blockIdx.x + gridDim.x - 1) / gridDim.x;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int64_t b = 0; b < my_batches; ++b) {
+                for (int t = 0; t < T; ++t) {
+                    const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));  // TreeRec
+                    const uint32_t blob_off16 = (uint32_t)raw.x, blob_bytes = (uint32_t)raw.y;
+                    mbar_wait(empty + stage, phase ^ 1u);
+                    mbar_expect_tx(full + stage, blob_bytes);
+                    bulk_g2s(ring + (size_t)stage * stage_bytes, f.blob + (size_t)blob_off16 * 16u, blob_bytes, full + stage);
+                    if (++stage == n_stages) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ---- consumers
+    const int lane = tid & 31;
+    const double Td = (double)T;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+        const int64_t row0 = b * S;
+        const int rows = (int)((a.n - row0) < (int64_t)S ? (a.n - row0) : (int64_t)S);
+        named_bar_sync(1, kConsumerThreads);  // previous batch fully consumed before xs is rewritten
+        const bool my_nan = load_tile<kConsumerThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+        const bool any_nan = named_bar_or(2, kConsumerThreads, my_nan);
+
+        double acc0[SPT], acc1[SPT];
+#pragma unroll
+        for (int i = 0; i < SPT; ++i) acc0[i] = acc1[i] = 0.0;
+
+        for (int t = 0; t < T; ++t) {
+            const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
+            const uint32_t values_off = (uint32_t)raw.z, depth = (uint32_t)raw.w;
+            mbar_wait(full + stage, phase);
+            const uint8_t* tb = ring + (size_t)stage * stage_bytes;
+            uint32_t vidx[SPT];
+            if (!any_nan)
+                descend_smem<SPT, kConsumerThreads, false>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, (int)depth, vidx);
+            else
+                descend_smem<SPT, kConsumerThreads, true>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, (int)depth, vidx);
+            const double2* vals = reinterpret_cast<const double2*>(tb + values_off);
+#pragma unroll
+            for (int i = 0; i < SPT; ++i) {
+                const double2 v = vals[vidx[i]];
+                acc0[i] += v.x;  // tree order, plain adds: SK/ensemble/_forest.py:714
+                acc1[i] += v.y;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty + stage);
+            if (++stage == n_stages) {
+                stage = 0;
+                phase ^= 1u;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < SPT; ++i) {
+            const int s = tid + i * kConsumerThreads;
+            if (s < rows) {
+                const double p0 = acc0[i] / Td, p1 = acc1[i] / Td;  // true divide: SK/ensemble/_forest.py:962
+                if (a.out) reinterpret_cast<double2*>(a.out)[row0 + s] = make_double2(p0, p1);
+                if (a.decision) a.decision[row0 + s] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
+            }
+        }
+    }
+}
+
+// =============================================================================== GLOBAL kernel
+// One 256-row tile per CTA, several CTAs per SM to cover L2 latency; nodes via the read-only path.
+template <bool NAN_AWARE>
+__device__ __forceinline__ uint32_t descend_global(const uint2* __restrict__ nodes, const float* __restrict__ xcol, int XS, int depth, uint32_t leaf_feat) {
+    uint2 nd = __ldg(nodes);
+    for (int d = 0; d < depth; ++d) {
+        const float x = xcol[(nd.y & kFeatMask) * XS];
+        nd = __ldg(nodes + step<NAN_AWARE>(nd, x));
+        // deep, ragged trees: stop as soon as the whole warp sits on leaves
+        if ((d & 3) == 3 && __all_sync(0xffffffffu, (nd.y & kFeatMask) == leaf_feat)) break;
+    }
+    return nd.x;
+}
+
+__global__ void __launch_bounds__(kTileThreads) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
+    constexpr int S = kTileThreads, XS = S + 1;
+    extern __shared__ __align__(128) uint8_t smem[];
+    float* xs = reinterpret_cast<float*>(smem);
+    const int F = f.n_features, T = f.n_trees, tid = threadIdx.x;
+    const int64_t row0 = (int64_t)blockIdx.x * S;
+    const int rows = (int)((a.n - row0) < (int64_t)S ? (a.n - row0) : (int64_t)S);
+    for (int i = tid; i < XS; i += kTileThreads) xs[F * XS + i] = 0.0f;
+    const bool my_nan = load_tile<kTileThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+    const bool any_nan = __syncthreads_or(my_nan) != 0;
+
+    double acc0 = 0.0, acc1 = 0.0;
+    for (int t = 0; t < T; ++t) {
+        const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
+        const uint8_t* tb = f.blob + (size_t)(uint32_t)raw.x * 16u;
+        const uint2* nodes = reinterpret_cast<const uint2*>(tb);
+        const uint32_t vidx = any_nan ? descend_global<true>(nodes, xs + tid, XS, raw.w, (uint32_t)F)
+                                      : descend_global<false>(nodes, xs + tid, XS, raw.w, (uint32_t)F);
+        const double2 v = __ldg(reinterpret_cast<const double2*>(tb + (uint32_t)raw.z) + vidx);
+        acc0 += v.x;
+        acc1 += v.y;
+    }
+    if (tid < rows) {
+        const double Td = (double)T;
+        const double p0 = acc0 / Td, p1 = acc1 / Td;
+        if (a.out) reinterpret_cast<double2*>(a.out)[row0 + tid] = make_double2(p0, p1);
+        if (a.decision) a.decision[row0 + tid] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
+    }
+}
+
+// ================================================================================ SPLIT kernels
+// grid.x = 256-row tiles, grid.y = tree chunks.  Each CTA brings its chunk's trees into a 2-stage
+// shared-memory ring by TMA and writes scratch[t][row] = (v0, v1) of the leaf row lands in.
+__global__ void __launch_bounds__(kTileThreads) k_split_descend(const ForestDev f, const ScoreArgs a, double2* __restrict__ scratch, const int trees_per_cta, const uint32_t stage_bytes, const int vec_ok) {
+    constexpr int S = kTileThreads, XS = S + 1;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+    float* xs = reinterpret_cast<float*>(smem + 128);
+    const int F = f.n_features, tid = threadIdx.x;
+    uint8_t* ring = smem + 128 + round_up((uint32_t)(F + 1) * XS * 4u, 128u);
+    const int t_lo = blockIdx.y * trees_per_cta;
+    const int t_hi = min(f.n_trees, t_lo + trees_per_cta);
+    const int64_t row0 = (int64_t)blockIdx.x * S;
+    const int rows = (int)((a.n - row0) < (int64_t)S ? (a.n - row0) : (int64_t)S);
+
+    if (tid == 0) {
+        for (int s = 0; s < kSplitStages; ++s) mbar_init(full + s, 1);
+        mbar_fence_init();
+        // prefetch the first trees while the tile loads (same thread inits and issues: ordered)
+        for (int s = 0; s < kSplitStages && t_lo + s < t_hi; ++s) {
+            const TreeRec tr = f.trees[t_lo + s];
+            mbar_expect_tx(full + s, tr.blob_bytes);
+            bulk_g2s(ring + (size_t)s * stage_bytes, f.blob + (size_t)tr.blob_off16 * 16u, tr.blob_bytes, full + s);
+        }
+    }
+    for (int i = tid; i < XS; i += kTileThreads) xs[F * XS + i] = 0.0f;
+    const bool my_nan = load_tile<kTileThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+    const bool any_nan = __syncthreads_or(my_nan) != 0;  // also publishes the mbarrier inits
+
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = t_lo; t < t_hi; ++t) {
+        const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
+        mbar_wait(full + stage, phase);
+        const uint8_t* tb = ring + (size_t)stage * stage_bytes;
+        uint32_t vidx[1];
+        if (!any_nan)
+            descend_smem<1, 0, false>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, raw.w, vidx);
+        else
+            descend_smem<1, 0, true>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, raw.w, vidx);
+        const double2 v = reinterpret_cast<const double2*>(tb + (uint32_t)raw.z)[vidx[0]];
+        if (tid < rows) scratch[(int64_t)t * a.n + row0 + tid] = v;
+        const int t_next = t + kSplitStages;
+        if (t_next < t_hi) {
+            __syncthreads();  // everyone is done reading this stage
+            if (tid == 0) {
+                const TreeRec tr = f.trees[t_next];
+                mbar_expect_tx(full + stage, tr.blob_bytes);
+                bulk_g2s(ring + (size_t)stage * stage_bytes, f.blob + (size_t)tr.blob_off16 * 16u, tr.blob_bytes, full + stage);
+            }
+        }
+        if (++stage == kSplitStages) {
+            stage = 0;
+            phase ^= 1u;
+        }
+    }
+}
+
+// out[row] = (sum over t = 0..T-1, in that order, of scratch[t][row]) / T
+__global__ void __launch_bounds__(128) k_split_reduce(const double2* __restrict__ scratch, const int T, const ScoreArgs a) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= a.n) return;
+    double acc0 = 0.0, acc1 = 0.0;
+    int t = 0;
+    for (; t + 4 <= T; t += 4) {
+        double2 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = scratch[(int64_t)(t + j) * a.n + row];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            acc0 += v[j].x;
+            acc1 += v[j].y;
+        }
+    }
+    for (; t < T; ++t) {
+        const double2 v = scratch[(int64_t)t * a.n + row];
+        acc0 += v.x;
+        acc1 += v.y;
+    }
+    const double Td = (double)T;
+    const double p0 = acc0 / Td, p1 = acc1 / Td;
+    if (a.out) reinterpret_cast<double2*>(a.out)[row] = make_double2(p0, p1);
+    if (a.decision) a.decision[row] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
+}
+
+// ------------------------------------------------------------------------------- host helpers
+struct StreamPlan {
+    bool ok = false;
+    int n_stages = 0;
+    uint32_t stage_bytes = 0;
+    uint32_t smem_bytes = 0;
+};
+
+StreamPlan plan_stream(const ccfd_forest* f, int spt) {
+    StreamPlan p;
+    const uint32_t S = kConsumerThreads * spt;
+    const uint32_t xs_bytes = round_up((uint32_t)(f->dev.n_features + 1) * (S + 1) * 4u, 128u);
+    p.stage_bytes = round_up(f->dev.max_tree_bytes, 128u);
+    const int64_t budget = (int64_t)f->smem_optin - 128 - (int64_t)xs_bytes;
+    if (budget < 2 * (int64_t)p.stage_bytes) return p;
+    p.n_stages = (int)(budget / p.stage_bytes);
+    if (p.n_stages > kMaxStages) p.n_stages = kMaxStages;
+    p.smem_bytes = 128 + xs_bytes + (uint32_t)p.n_stages * p.stage_bytes;
+    p.ok = true;
+    return p;
+}
+
+uint32_t tile_xs_bytes(const ccfd_forest* f) { return round_up((uint32_t)(f->dev.n_features + 1) * (kTileThreads + 1) * 4u, 128u); }
+
+bool split_ok(const ccfd_forest* f, uint32_t* smem_bytes) {
+    const uint32_t stage = round_up(f->dev.max_tree_bytes, 128u);
+    const uint32_t need = 128 + tile_xs_bytes(f) + kSplitStages * stage;
+    if (smem_bytes) *smem_bytes = need;
+    // keep it small enough for 2 CTAs per SM so short requests overlap
+    return need <= (uint32_t)f->smem_optin / 2;
+}
+
+}  // namespace
+
+int ccfd_kernels_init(ccfd_forest* f) {
+    DeviceGuard guard(f->device);
+    CCFD_CUDA(cudaDeviceGetAttribute(&f->sm_count, cudaDevAttrMultiProcessorCount, f->device));
+    CCFD_CUDA(cudaDeviceGetAttribute(&f->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, f->device));
+    int major = 0;
+    CCFD_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, f->device));
+    if (major != 10) return ccfd_fail(CCFD_EUNSUPPORTED, "libccfd_rf is built for sm_100a (B200); device %d has compute capability major %d", f->device, major);
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_split_descend, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_global, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    f->info.stream_kernel_ok = (plan_stream(f, 1).ok && split_ok(f, nullptr)) ? 1 : 0;
+    return CCFD_OK;
+}
+
+uint32_t ccfd_pick_kernel(const ccfd_forest* f, int64_t n) {
+    if (!f->info.stream_kernel_ok) return CCFD_KERNEL_GLOBAL;
+    return n >= 16384 ? CCFD_KERNEL_STREAM : CCFD_KERNEL_SPLIT;
+}
+
+int64_t ccfd_split_scratch_bytes(const ccfd_forest* f, int64_t n) { return n * (int64_t)f->dev.n_trees * (int64_t)sizeof(double2); }
+
+int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel, void* scratch, cudaStream_t stream) {
+    if (a.n <= 0) return CCFD_OK;
+    if (a.out && (reinterpret_cast<uintptr_t>(a.out) & 15u)) return ccfd_fail(CCFD_EINVAL, "out must be 16-byte aligned");
+    if (reinterpret_cast<uintptr_t>(a.X) & 3u) return ccfd_fail(CCFD_EINVAL, "X must be 4-byte aligned");
+    const int vec_ok = (a.ld == f->dev.n_features) && ((reinterpret_cast<uintptr_t>(a.X) & 15u) == 0);
+    if (kernel == CCFD_KERNEL_AUTO) kernel = ccfd_pick_kernel(f, a.n);
+
+    if (kernel == CCFD_KERNEL_STREAM) {
+        // two rows per thread once there is enough work to fill the chip twice over
+        int spt = (a.n >= (int64_t)f->sm_count * kConsumerThreads * 4) ? 2 : 1;
+        StreamPlan p = plan_stream(f, spt);
+        if (!p.ok && spt == 2) p = plan_stream(f, spt = 1);
+        if (!p.ok) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the STREAM kernel", f->dev.max_tree_bytes);
+        const int64_t S = (int64_t)kConsumerThreads * spt;
+        const int64_t n_batches = (a.n + S - 1) / S;
+        const int grid = (int)(n_batches < f->sm_count ? n_batches : f->sm_count);
+        // the 16-byte alignment of each batch's first row holds because S * F * 4 is a multiple of 16
+        if (spt == 2)
+            k_stream<2><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, p.stage_bytes, vec_ok);
+        else
+            k_stream<1><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, p.stage_bytes, vec_ok);
+    } else if (kernel == CCFD_KERNEL_SPLIT) {
+        uint32_t smem_bytes = 0;
+        if (!split_ok(f, &smem_bytes)) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the SPLIT kernel", f->dev.max_tree_bytes);
+        if (!scratch) return ccfd_fail(CCFD_EINVAL, "SPLIT kernel needs scratch");
+        const int64_t tiles = (a.n + kTileThreads - 1) / kTileThreads;
+        if (tiles > 0x7FFFFFFFll) return ccfd_fail(CCFD_EINVAL, "too many rows for one launch");
+        // aim at two CTAs per SM over the whole grid
+        int64_t chunks = (2 * (int64_t)f->sm_count + tiles - 1) / tiles;
+        if (chunks > f->dev.n_trees) chunks = f->dev.n_trees;
+        if (chunks < 1) chunks = 1;
+        const int trees_per_cta = (int)((f->dev.n_trees + chunks - 1) / chunks);
+        chunks = (f->dev.n_trees + trees_per_cta - 1) / trees_per_cta;
+        if (chunks > 65535) return ccfd_fail(CCFD_EINVAL, "too many tree chunks");
+        const uint32_t stage_bytes = round_up(f->dev.max_tree_bytes, 128u);
+        dim3 grid((unsigned)tiles, (unsigned)chunks);
+        k_split_descend<<<grid, kTileThreads, smem_bytes, stream>>>(f->dev, a, static_cast<double2*>(scratch), trees_per_cta, stage_bytes, vec_ok);
+        k_split_reduce<<<(unsigned)((a.n + 127) / 128), 128, 0, stream>>>(static_cast<const double2*>(scratch), f->dev.n_trees, a);
+    } else if (kernel == CCFD_KERNEL_GLOBAL) {
+        const int64_t tiles = (a.n + kTileThreads - 1) / kTileThreads;
+        if (tiles > 0x7FFFFFFFll) return ccfd_fail(CCFD_EINVAL, "too many rows for one launch");
+        k_global<<<(unsigned)tiles, kTileThreads, tile_xs_bytes(f), stream>>>(f->dev, a, vec_ok);
+    } else {
+        return ccfd_fail(CCFD_EINVAL, "unknown kernel selector 0x%x", kernel);
+    }
+    CCFD_CUDA(cudaGetLastError());
+    return CCFD_OK;
+}

@@ -1,0 +1,241 @@
+"""Host side of the scoring path: the Seldon model class and thin handle wrappers.
+
+``CcfdForestModel`` is what goes into the demo's Seldon deployment in place of
+the class inside ``nakfour/modelfull`` (reference deploy/model/modelfull.json:20-44):
+the Seldon Python wrapper calls ``predict(X, feature_names)`` with the decoded
+request matrix and expects class probabilities back, column order
+``classes_ = [0, 1]`` (non-fraud, fraud).  Everything numeric happens in
+libccfd_rf on the GPU; there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import pickle
+import threading
+
+import numpy as np
+
+from . import _lib
+from .converter import ForestArrays, from_sklearn
+from .synth import FEATURE_NAMES
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def validate_X(X, n_features: int) -> np.ndarray:
+    """Mirror ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625).
+
+    Any real dtype / memory order / nested list is accepted and cast to a C-ordered
+    float32 matrix; NaN is allowed (trees route it by missing_go_to_left); 1-D
+    input, zero rows, a wrong feature count and +-inf (or a float64 that overflows
+    float32) raise ValueError, as scikit-learn does.
+    """
+    X = np.asarray(X)
+    if X.dtype == object or X.dtype.kind not in "fiub":
+        try:
+            X = X.astype(np.float64)
+        except (TypeError, ValueError) as e:
+            raise ValueError(f"could not convert input to float: {e}") from None
+    if X.ndim != 2:
+        raise ValueError(f"Expected 2D array, got {X.ndim}D array instead. Reshape your data using "
+                         "array.reshape(1, -1) if it contains a single sample.")
+    if X.shape[0] < 1:
+        raise ValueError(f"Found array with 0 sample(s) (shape={X.shape}) while a minimum of 1 is required.")
+    if X.shape[1] != n_features:
+        raise ValueError(f"X has {X.shape[1]} features, but the forest is expecting {n_features} features as input.")
+    with np.errstate(over="ignore"):
+        X32 = np.ascontiguousarray(X, dtype=np.float32)
+    if np.isinf(X32).any():
+        raise ValueError("Input X contains infinity or a value too large for dtype('float32').")
+    return X32
+
+
+class Forest:
+    """A forest resident on one GPU (opaque ``ccfd_forest`` handle)."""
+
+    def __init__(self, arrays: ForestArrays, device: int = 0):
+        self._h = ctypes.c_void_p()
+        L = _lib.lib()
+        a = arrays
+        keep = [np.ascontiguousarray(x) for x in
+                (a.tree_offsets, a.feature, a.threshold, a.left, a.right, a.missing_go_to_left, a.value)]
+        d = _lib.ForestDesc(a.n_trees, a.n_features, a.n_classes, 0, *[_ptr(x) for x in keep])
+        _lib.check(L.ccfd_forest_create(ctypes.byref(d), int(device), ctypes.byref(self._h)))
+        del keep  # the library copied everything
+        info = _lib.ForestInfo()
+        _lib.check(L.ccfd_forest_get_info(self._h, ctypes.byref(info)))
+        self.info = {k: getattr(info, k) for k, _ in _lib.ForestInfo._fields_}
+        self.n_features = a.n_features
+        self.n_trees = a.n_trees
+        self.device = int(device)
+
+    @property
+    def handle(self):
+        if not self._h:
+            raise RuntimeError("forest is closed")
+        return self._h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.lib().ccfd_forest_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    __del__ = close
+
+    # -- host buffers ---------------------------------------------------------------------
+    def predict_proba(self, X32: np.ndarray, kernel: str = "auto", out: np.ndarray | None = None) -> np.ndarray:
+        """Validated float32 rows in host memory (unit column stride) -> (n, 2) float64."""
+        n, ld = X32.shape[0], X32.strides[0] // 4
+        if out is None:
+            out = np.empty((n, 2), dtype=np.float64)
+        _lib.check(_lib.lib().ccfd_predict_proba(self.handle, _ptr(X32), n, ld, _ptr(out), _lib.KERNELS[kernel], None))
+        return out
+
+    def decide(self, X32: np.ndarray, threshold: float = 0.5, ge: bool = False, want_proba: bool = False,
+               kernel: str = "auto"):
+        n, ld = X32.shape[0], X32.strides[0] // 4
+        dec = np.empty(n, dtype=np.uint8)
+        out = np.empty((n, 2), dtype=np.float64) if want_proba else None
+        _lib.check(_lib.lib().ccfd_predict_decision(self.handle, _ptr(X32), n, ld, _ptr(out) if want_proba else None,
+                                                    _ptr(dec), float(threshold), int(ge), _lib.KERNELS[kernel], None))
+        return (dec.astype(bool), out) if want_proba else dec.astype(bool)
+
+    # -- device buffers (raw pointers, e.g. torch tensors' data_ptr()) -----------------------
+    def predict_proba_device(self, x_ptr: int, n: int, ld: int, out_ptr: int, stream: int = 0, kernel: str = "auto",
+                             sync: bool = True):
+        flags = _lib.DEVICE_PTRS | _lib.KERNELS[kernel] | (0 if sync else _lib.ASYNC)
+        _lib.check(_lib.lib().ccfd_predict_proba(self.handle, ctypes.c_void_p(x_ptr), n, ld, ctypes.c_void_p(out_ptr),
+                                                 flags, ctypes.c_void_p(stream)))
+
+    def decide_device(self, x_ptr: int, n: int, ld: int, dec_ptr: int, out_ptr: int = 0, threshold: float = 0.5,
+                      ge: bool = False, stream: int = 0, kernel: str = "auto", sync: bool = True):
+        flags = _lib.DEVICE_PTRS | _lib.KERNELS[kernel] | (0 if sync else _lib.ASYNC)
+        _lib.check(_lib.lib().ccfd_predict_decision(
+            self.handle, ctypes.c_void_p(x_ptr), n, ld, ctypes.c_void_p(out_ptr) if out_ptr else None,
+            ctypes.c_void_p(dec_ptr), float(threshold), int(ge), flags, ctypes.c_void_p(stream)))
+
+
+class Session:
+    """Pinned ring of request slots with pre-captured CUDA graphs (latency path)."""
+
+    def __init__(self, forest: Forest, max_batch: int = 1024, n_slots: int = 4):
+        self.forest, self.max_batch, self.n_slots = forest, int(max_batch), int(n_slots)
+        self._h = ctypes.c_void_p()
+        L = _lib.lib()
+        _lib.check(L.ccfd_session_create(forest.handle, self.max_batch, self.n_slots, ctypes.byref(self._h)))
+        self.x, self.p = [], []
+        for s in range(self.n_slots):
+            xp, pp = ctypes.POINTER(ctypes.c_float)(), ctypes.POINTER(ctypes.c_double)()
+            _lib.check(L.ccfd_session_buffers(self._h, s, ctypes.byref(xp), ctypes.byref(pp)))
+            self.x.append(np.ctypeslib.as_array(xp, shape=(self.max_batch, forest.n_features)))
+            self.p.append(np.ctypeslib.as_array(pp, shape=(self.max_batch, 2)))
+
+    def submit(self, slot: int, n_rows: int):
+        _lib.check(_lib.lib().ccfd_session_submit(self._h, slot, n_rows))
+
+    def wait(self, slot: int):
+        _lib.check(_lib.lib().ccfd_session_wait(self._h, slot))
+
+    def score(self, slot: int, rows: np.ndarray) -> np.ndarray:
+        """Copy rows into the slot, run its graph, return a copy of the probabilities."""
+        n = rows.shape[0]
+        self.x[slot][:n] = rows
+        self.submit(slot, n)
+        self.wait(slot)
+        return self.p[slot][:n].copy()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.x, self.p = [], []
+            _lib.lib().ccfd_session_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    __del__ = close
+
+
+def load_model_file(path: str) -> ForestArrays:
+    """``.npz`` written by ForestArrays.save, or a pickle/joblib of a fitted RandomForestClassifier."""
+    if path.endswith(".npz"):
+        return ForestArrays.load(path)
+    try:
+        import joblib
+
+        obj = joblib.load(path)
+    except Exception:
+        with open(path, "rb") as fh:
+            obj = pickle.load(fh)
+    return from_sklearn(obj)
+
+
+class CcfdForestModel:
+    """Seldon MODEL class: ``predict(X, feature_names) -> (n, 2) float64 [p_nonfraud, p_fraud]``.
+
+    Configuration keeps the demo's environment-variable idiom (reference
+    deploy/router.yaml:54-70): ``CCFD_MODEL_PATH`` (forest file), ``CCFD_DEVICE``
+    (GPU index), ``CCFD_SESSION_MAX_BATCH`` (requests up to this many rows take the
+    CUDA-graph path; 0 disables it), ``FRAUD_THRESHOLD`` (same name and default as the
+    router's).  A fitted forest or a ForestArrays can also be passed directly.
+    """
+
+    class_names = ["proba_0", "proba_1"]
+
+    def __init__(self, model=None, device: int | None = None, session_max_batch: int | None = None):
+        if model is None:
+            path = os.environ.get("CCFD_MODEL_PATH")
+            if not path:
+                raise ValueError("no model given and CCFD_MODEL_PATH is not set")
+            model = load_model_file(path)
+        arrays = model if isinstance(model, ForestArrays) else from_sklearn(model)
+        device = int(os.environ.get("CCFD_DEVICE", "0")) if device is None else device
+        self.forest = Forest(arrays, device)
+        self.n_features_in_ = arrays.n_features
+        self.classes_ = np.arange(arrays.n_classes)
+        self.threshold = float(os.environ.get("FRAUD_THRESHOLD", "0.5"))
+        smb = int(os.environ.get("CCFD_SESSION_MAX_BATCH", "1024")) if session_max_batch is None else session_max_batch
+        self._session = Session(self.forest, smb, n_slots=2) if smb > 0 else None
+        self._lock = threading.Lock()
+        self._slot = 0
+        self._last = None
+
+    def predict(self, X, feature_names=None, meta=None):
+        """The Seldon wrapper passes the names positionally; like scikit-learn on a forest fitted
+        from an ndarray, they are not used to reorder columns."""
+        X32 = validate_X(X, self.n_features_in_)
+        n = X32.shape[0]
+        if self._session is not None and n <= self._session.max_batch:
+            with self._lock:
+                slot = self._slot
+                self._slot = (slot + 1) % self._session.n_slots
+                P = self._session.score(slot, X32)
+        else:
+            P = self.forest.predict_proba(X32)
+        self._last = (X32[-1].copy(), P[-1].copy())
+        return P
+
+    def decide(self, X, threshold: float | None = None, ge: bool = False):
+        """Router rule (reference deploy/router.yaml:69-70): fraud iff p_fraud > FRAUD_THRESHOLD."""
+        X32 = validate_X(X, self.n_features_in_)
+        return self.forest.decide(X32, self.threshold if threshold is None else threshold, ge)
+
+    def metrics(self):
+        """Gauges the shipped ModelPrediction board plots (reference deploy/grafana/ModelPrediction.json:96,104,211,322)."""
+        if self._last is None:
+            return []
+        x, p = self._last
+        g = lambda k, v: {"type": "GAUGE", "key": k, "value": float(v)}  # noqa: E731
+        out = [g("proba_1", p[1])]
+        if self.n_features_in_ == len(FEATURE_NAMES):
+            out += [g("Amount", x[29]), g("V17", x[17]), g("V10", x[10])]
+        return out
+
+    def tags(self):
+        return {"backend": "libccfd_rf/sm_100a", "n_trees": self.forest.n_trees, "device": self.forest.device}
+
+    def close(self):
+        if self._session is not None:
+            self._session.close()
+            self._session = None
+        self.forest.close()

@@ -1,0 +1,145 @@
+/* libccfd_rf — C ABI of the B200 random-forest scoring path.
+ *
+ * This is the drop-in boundary for ONE path of the credit-card-fraud demo: the
+ * fraud model's batched RandomForestClassifier.predict_proba behind the Seldon
+ * model node `modelfull` (reference deploy/model/modelfull.json:20-44, reached
+ * at SELDON_URL + SELDON_ENDPOINT, reference deploy/router.yaml:65-68).  The
+ * reference ships that node as an opaque Python image, so there is no FFI in
+ * the reference to copy; the entry points below are what a Python model class
+ * (ctypes) binds in place of scikit-learn's calls.  SK/ is
+ * scikit-learn 1.9.0's source tree, where the replaced arithmetic lives.
+ *
+ * Conventions: every function returns CCFD_OK (0) or a negative CCFD_E* code,
+ * never throws, never aborts; ccfd_last_error() returns a thread-local message
+ * for the last failure on the calling thread.  Handles are opaque and owned by
+ * the library; bulk buffers are owned by the caller unless stated.  Plain
+ * pointers and sizes only: no C++ or torch types cross this line.
+ */
+#ifndef CCFD_RF_H
+#define CCFD_RF_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define CCFD_API __attribute__((visibility("default")))
+#else
+#define CCFD_API
+#endif
+
+#define CCFD_OK 0
+#define CCFD_EINVAL (-1)       /* bad argument or malformed forest  -> Python ValueError */
+#define CCFD_ECUDA (-2)        /* CUDA runtime failure (message carries cudaGetErrorString) */
+#define CCFD_ENOMEM (-3)       /* host or device allocation failed */
+#define CCFD_EUNSUPPORTED (-4) /* valid input this build does not handle (e.g. n_classes != 2) */
+#define CCFD_ESTATE (-5)       /* call made in the wrong state (e.g. wait on an idle slot) */
+
+/* flags for ccfd_predict_proba / ccfd_predict_decision */
+#define CCFD_DEVICE_PTRS 0x1u  /* X and out are device pointers on the forest's device (default: host) */
+#define CCFD_ASYNC 0x2u        /* device pointers only: enqueue on `stream` and return without waiting */
+/* kernel choice; AUTO picks by forest and batch size.  The others exist so
+ * tests and the bench can pin a kernel; they fail with CCFD_EUNSUPPORTED when
+ * the forest does not fit that kernel. */
+#define CCFD_KERNEL_AUTO 0x000u
+#define CCFD_KERNEL_STREAM 0x100u /* throughput: rows resident in shared memory, trees streamed through it */
+#define CCFD_KERNEL_SPLIT 0x200u  /* latency: (row tile x tree chunk) grid, per-tree scratch, ordered reduce */
+#define CCFD_KERNEL_GLOBAL 0x300u /* any forest: nodes read from global memory / L2 */
+#define CCFD_KERNEL_MASK 0xF00u
+
+typedef struct ccfd_forest ccfd_forest;   /* immutable after create; shareable across threads */
+typedef struct ccfd_session ccfd_session; /* single producer / single consumer */
+
+/* A fitted forest as plain structure-of-arrays, all host pointers, all copied
+ * by ccfd_forest_create.  Replaces what predict_proba reads from
+ * RandomForestClassifier.estimators_[t].tree_ (SK/tree/_tree.pyx:656-765,
+ * Node fields SK/tree/_tree.pxd:15-25).  Node indices are tree-local. */
+typedef struct ccfd_forest_desc {
+    int32_t n_trees;
+    int32_t n_features;            /* 1..255; the demo's model has 30 (Time, V1..V28, Amount) */
+    int32_t n_classes;             /* this build: 2 (non-fraud, fraud) */
+    int32_t reserved;              /* must be 0 */
+    const int64_t* tree_offsets;   /* [n_trees+1] node range of each tree in the arrays below */
+    const int32_t* feature;        /* [total] split feature; ignored at leaves */
+    const float* threshold;        /* [total] LARGEST fp32 <= sklearn's fp64 threshold (see converter) */
+    const int32_t* left;           /* [total] left child, -1 at leaves  (x <= threshold, SK/tree/_tree.pyx:989) */
+    const int32_t* right;          /* [total] right child, -1 at leaves */
+    const uint8_t* missing_go_to_left; /* [total] NaN routing (SK/tree/_tree.pyx:984-988) */
+    const double* value;           /* [total * n_classes] class fractions at every node; leaves are read */
+} ccfd_forest_desc;
+
+typedef struct ccfd_forest_info {
+    int32_t n_trees, n_features, n_classes, max_depth;
+    int64_t n_nodes;       /* reachable nodes kept */
+    int64_t n_leaves;
+    int64_t model_bytes;   /* packed device bytes: what one launch reads of the model */
+    int64_t max_tree_bytes;
+    int32_t device;
+    int32_t stream_kernel_ok; /* 1 if every tree fits the shared-memory stage of the STREAM/SPLIT kernels */
+} ccfd_forest_info;
+
+/* Number of CUDA devices, or a negative CCFD_E* code. */
+CCFD_API int ccfd_device_count(void);
+/* Thread-local message of the last failure on this thread ("" if none). */
+CCFD_API const char* ccfd_last_error(void);
+
+/* Validate, re-lay-out (breadth-first, sibling-adjacent, 8-byte nodes) and upload.
+ * Replaces: unpickling the forest inside the model image (reference
+ * deploy/model/modelfull.json:24) — the library's equivalent of model load. */
+CCFD_API int ccfd_forest_create(const ccfd_forest_desc* desc, int device, ccfd_forest** out);
+CCFD_API int ccfd_forest_destroy(ccfd_forest* forest);
+/* The same validation and re-layout without a GPU: writes the packed image the kernels read
+ * (all tree blobs back to back) and 4 uint32 per tree {offset/16, bytes, leaf-value offset,
+ * depth}.  Call with blob == NULL and tree_recs == NULL to learn *blob_bytes first.  Lets a
+ * deployment build step (and the CPU tests) check a forest before it reaches a GPU; has no
+ * counterpart in scikit-learn, whose trees are scored in their fitted layout. */
+CCFD_API int ccfd_forest_pack(const ccfd_forest_desc* desc, void* blob, int64_t blob_capacity, uint32_t* tree_recs,
+                              int64_t* blob_bytes);
+CCFD_API int ccfd_forest_get_info(const ccfd_forest* forest, ccfd_forest_info* info);
+
+/* out[i, 0..1] = mean over trees of the leaf class fractions of row i, float64,
+ * summed in tree order 0..T-1 and then divided by T.
+ * Replaces ForestClassifier.predict_proba (SK/ensemble/_forest.py:921-967) with
+ * everything under it: Tree._apply_dense (SK/tree/_tree.pyx:954-996), the leaf
+ * gather (SK/tree/_tree.pyx:939-945) and _accumulate_prediction
+ * (SK/ensemble/_forest.py:704-717).
+ *   X    n rows of n_features float32, row stride `ld` floats (ld >= n_features).
+ *        NaN is routed by missing_go_to_left; +-inf is the caller's to reject
+ *        (sklearn raises ValueError before scoring, SK/ensemble/_forest.py:606-625).
+ *   out  n * 2 float64, row-major.
+ *   stream  a cudaStream_t (NULL = the default stream).
+ * Host pointers: the call copies in chunks, overlapping copies with scoring,
+ * and returns when `out` is complete (pinned memory makes the copies fast).
+ * Re-entrant for device pointers; host-pointer calls on one forest serialise. */
+CCFD_API int ccfd_predict_proba(ccfd_forest* forest, const float* X, int64_t n, int64_t ld, double* out,
+                       uint32_t flags, void* stream);
+
+/* Same scoring, plus the router's rule fused into the epilogue: decision[i] = 1
+ * iff p_fraud (op) threshold, op being `>` (ge == 0) or `>=` (ge != 0).
+ * Replaces the Drools rule on the returned probability against
+ * FRAUD_THRESHOLD = 0.5 (reference deploy/router.yaml:69-70, README.md:427).
+ * `out` may be NULL to emit decisions only (bulk rescoring: 1 byte per row). */
+CCFD_API int ccfd_predict_decision(ccfd_forest* forest, const float* X, int64_t n, int64_t ld, double* out,
+                          uint8_t* decision, double threshold, int ge, uint32_t flags, void* stream);
+
+/* Latency path: `n_slots` pinned host slots of `max_batch` rows, each with its
+ * own device buffers and a pre-captured CUDA graph (copy in, score, copy out).
+ * Replaces the per-request work of the Seldon wrapper around predict()
+ * (requests arriving at reference deploy/router.yaml:65-68): the caller writes
+ * rows straight into the slot and no allocation or Python happens per request. */
+CCFD_API int ccfd_session_create(ccfd_forest* forest, int64_t max_batch, int32_t n_slots, ccfd_session** out);
+CCFD_API int ccfd_session_destroy(ccfd_session* session);
+/* Library-owned pinned buffers of slot `slot`: x (max_batch * n_features fp32,
+ * dense rows) to write, p (max_batch * 2 fp64) to read after wait. */
+CCFD_API int ccfd_session_buffers(ccfd_session* session, int32_t slot, float** x, double** p);
+/* Score the first n_rows rows of the slot (1 <= n_rows <= max_batch); returns at once. */
+CCFD_API int ccfd_session_submit(ccfd_session* session, int32_t slot, int64_t n_rows);
+/* Block until the slot's results are visible in its p buffer. */
+CCFD_API int ccfd_session_wait(ccfd_session* session, int32_t slot);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCFD_RF_H */

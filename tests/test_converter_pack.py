@@ -1,0 +1,118 @@
+"""Converter + library re-layout, checked on the CPU against scikit-learn's outputs."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import packed_emulator
+from conftest import bits, load_golden
+from ccfd_demo_summit_b200 import _lib, converter
+
+
+def _fa(raw):
+    return converter.from_arrays(raw.tree_offsets, raw.left, raw.right, raw.feature, raw.threshold,
+                                 raw.missing_go_to_left, raw.value, raw.n_features, raw.n_classes)
+
+
+def test_floor_to_float32_is_largest_float32_not_above():
+    rng = np.random.default_rng(0)
+    a = rng.standard_normal(20000).astype(np.float32)
+    b = np.nextafter(a, np.float32(np.inf))
+    t = (a.astype(np.float64) + b.astype(np.float64)) / 2  # midpoints, like SK/tree/_splitter.pyx:459-461
+    t = np.concatenate([t, a.astype(np.float64), [np.inf, 0.0, -0.0, 1e-46, -1e-46, 3.5e38]])
+    f = converter.floor_to_float32(t)
+    assert f.dtype == np.float32
+    assert np.all(f.astype(np.float64) <= t)
+    up = np.nextafter(f, np.float32(np.inf))
+    finite = np.isfinite(t)
+    assert np.all(up[finite].astype(np.float64) > t[finite])
+    assert f[len(a) * 2] == np.inf
+
+
+def test_floored_threshold_is_equivalent_for_every_float32_neighbour():
+    raw, X, P, _ = load_golden("small_hard")
+    t = raw.threshold[raw.left != -1]
+    f = converter.floor_to_float32(t)
+    for x in (f, np.nextafter(f, np.float32(np.inf)), np.nextafter(f, np.float32(-np.inf))):
+        assert np.array_equal(x.astype(np.float64) <= t, x <= f)
+
+
+def test_packed_walk_matches_sklearn_bitwise(golden):
+    name, raw, X, P, _ = golden
+    fa = _fa(raw)
+    blob, recs = packed_emulator.pack(fa)
+    got = packed_emulator.predict_proba(blob, recs, fa.n_features, np.ascontiguousarray(X, dtype=np.float32))
+    assert np.array_equal(bits(got), bits(P)), name
+
+
+def test_pack_layout_invariants():
+    raw, *_ = load_golden("bestfirst")  # best-first builder: source nodes are not in pre-order
+    fa = _fa(raw)
+    blob, recs = packed_emulator.pack(fa)
+    assert blob.nbytes % 16 == 0
+    for t, (off16, nbytes, values_off, depth) in enumerate(recs):
+        assert nbytes % 16 == 0 and values_off % 16 == 0
+        n_src = int(raw.tree_offsets[t + 1] - raw.tree_offsets[t])
+        n_leaves = (int(nbytes) - int(values_off)) // 16
+        assert n_leaves == (n_src + 1) // 2
+        nodes = blob[int(off16) * 16: int(off16) * 16 + n_src * 8].view(np.uint32).reshape(-1, 2)
+        internal = (nodes[:, 1] & 0xFF) != fa.n_features
+        child = nodes[internal, 1] >> 9
+        # siblings adjacent, children after parents, every slot referenced exactly once
+        assert np.array_equal(np.sort(np.concatenate([child, child + 1])), np.arange(1, n_src))
+        assert np.all(child > np.nonzero(internal)[0])
+        assert np.array_equal(nodes[~internal, 1] >> 9, np.nonzero(~internal)[0])  # leaves point at themselves
+
+
+def test_from_sklearn_reads_a_fitted_forest():
+    from sklearn.ensemble import RandomForestClassifier
+
+    from ccfd_demo_summit_b200 import synth
+    from oracle import rf_oracle
+
+    X, y = synth.make_dataset(1500, seed=3)
+    rf = RandomForestClassifier(n_estimators=5, max_depth=5, random_state=0).fit(X, y)
+    fa = converter.from_sklearn(rf)
+    raw = rf_oracle.extract_raw(rf)
+    assert fa.n_trees == 5 and fa.n_features == 30 and fa.n_classes == 2
+    assert np.array_equal(fa.tree_offsets, raw.tree_offsets)
+    blob, recs = packed_emulator.pack(fa)
+    rf.n_jobs = 1
+    assert np.array_equal(bits(packed_emulator.predict_proba(blob, recs, 30, X[:500])), bits(rf.predict_proba(X[:500])))
+
+
+@pytest.mark.parametrize("breakage", ["cycle", "feature", "one_child", "nan_thr", "offsets", "classes", "child_range"])
+def test_malformed_forests_are_rejected_with_valueerror(breakage):
+    raw, *_ = load_golden("stumps")
+    fa = _fa(raw)
+    if breakage == "cycle":
+        fa.left[0] = 0
+    elif breakage == "feature":
+        fa.feature[0] = 30
+    elif breakage == "one_child":
+        fa.left[0] = -1
+    elif breakage == "nan_thr":
+        fa.threshold[0] = np.nan
+    elif breakage == "offsets":
+        fa.tree_offsets[1] = 0
+    elif breakage == "classes":
+        fa.n_classes = 3
+    elif breakage == "child_range":
+        fa.right[0] = 7
+    expect = _lib.CcfdError if breakage == "classes" else ValueError
+    with pytest.raises(expect):
+        packed_emulator.pack(fa)
+
+
+def test_library_exports_every_declared_symbol():
+    import os
+    import re
+
+    header = open(os.path.join(os.path.dirname(_lib.PKG), "include", "ccfd_rf.h")).read()
+    declared = set(re.findall(r"CCFD_API\s+[\w \*]+?\b(ccfd_\w+)\s*\(", header))
+    bound = {name for name, _, _ in _lib.SYMBOLS}
+    assert declared == bound, declared ^ bound
+    L = _lib.lib()
+    for name in declared:
+        assert getattr(L, name) is not None
+    assert isinstance(L.ccfd_last_error(), bytes)

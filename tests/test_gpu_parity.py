@@ -1,0 +1,223 @@
+"""GPU parity: the CUDA path through the C ABI against scikit-learn's outputs (golden fixtures),
+the oracle, and scikit-learn itself on the box.  Integer/bit work: float64 results must be
+bit-identical (tolerance 0); north_star asks |dp| <= 1e-6 and exact decisions at 0.5."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_DIR, bits, load_golden
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+KERNELS = ["auto", "stream", "split", "global"]
+
+
+@pytest.fixture(scope="module")
+def ccfd():
+    import ccfd_demo_summit_b200 as pkg
+    from ccfd_demo_summit_b200 import model  # raises if libccfd_rf.so is missing: no fallback
+
+    assert torch.cuda.is_available()
+    return pkg, model
+
+
+def _fa(raw):
+    from ccfd_demo_summit_b200 import converter
+
+    return converter.from_arrays(raw.tree_offsets, raw.left, raw.right, raw.feature, raw.threshold,
+                                 raw.missing_go_to_left, raw.value, raw.n_features, raw.n_classes)
+
+
+def _score_device(forest, X32, kernel="auto", ld=None, misalign=False):
+    n, F = X32.shape
+    ld = F if ld is None else ld
+    buf = torch.zeros(n * ld + 4, dtype=torch.float32, device="cuda")
+    off = 1 if misalign else 0
+    view = buf[off: off + n * ld].view(n, ld)
+    view[:, :F] = torch.from_numpy(X32).cuda()
+    out = torch.full((n, 2), -1.0, dtype=torch.float64, device="cuda")
+    forest.predict_proba_device(view.data_ptr(), n, ld, out.data_ptr(), torch.cuda.current_stream().cuda_stream, kernel)
+    return out.cpu().numpy()
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_golden_bitwise_device_pointers(ccfd, golden, kernel):
+    _, model = ccfd
+    name, raw, X, P, _ = golden
+    forest = model.Forest(_fa(raw))
+    got = _score_device(forest, np.ascontiguousarray(X, dtype=np.float32), kernel)
+    assert np.array_equal(bits(got), bits(P)), (name, kernel, np.abs(got - P).max())
+    assert np.array_equal(got[:, 1] > 0.5, P[:, 1] > 0.5)
+    forest.close()
+
+
+@pytest.mark.parametrize("kernel", ["stream", "split", "global"])
+def test_strided_and_misaligned_rows(ccfd, kernel):
+    _, model = ccfd
+    raw, X, P, _ = load_golden("small_hard")
+    forest = model.Forest(_fa(raw))
+    assert np.array_equal(bits(_score_device(forest, X, kernel, ld=37)), bits(P))
+    assert np.array_equal(bits(_score_device(forest, X, kernel, misalign=True)), bits(P))
+    forest.close()
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 32, 33, 255, 256, 257, 511, 512, 513, 1023, 1024, 1025, 1500])
+def test_ragged_batch_sizes_all_kernels(ccfd, n):
+    _, model = ccfd
+    raw, X, P, _ = load_golden("small_hard")
+    forest = model.Forest(_fa(raw))
+    for kernel in ("stream", "split", "global"):
+        assert np.array_equal(bits(_score_device(forest, X[:n], kernel)), bits(P[:n])), (n, kernel)
+    forest.close()
+
+
+def test_host_pointer_path_and_oracle(ccfd, golden):
+    from oracle import rf_oracle
+
+    _, model = ccfd
+    name, raw, X, P, _ = golden
+    forest = model.Forest(_fa(raw))
+    X32 = np.ascontiguousarray(X, dtype=np.float32)
+    got = forest.predict_proba(X32)
+    assert np.array_equal(bits(got), bits(P)), name
+    assert np.array_equal(bits(got), bits(rf_oracle.predict_proba_c(raw, X32))), name
+    forest.close()
+
+
+def test_fused_decision_matches_threshold_rule(ccfd):
+    _, model = ccfd
+    raw, X, P, _ = load_golden("deep")  # pure leaves: p is k/T, ties at the threshold really happen
+    forest = model.Forest(_fa(raw))
+    thr = float(np.median(P[:, 1][P[:, 1] > 0])) if (P[:, 1] > 0).any() else 0.5
+    for t in (0.5, thr, 0.0, 1.0):
+        for kernel in ("stream", "split", "global"):
+            d_gt, p = forest.decide(X, t, ge=False, want_proba=True, kernel=kernel)
+            d_ge = forest.decide(X, t, ge=True, kernel=kernel)
+            assert np.array_equal(d_gt, P[:, 1] > t) and np.array_equal(d_ge, P[:, 1] >= t), (t, kernel)
+            assert np.array_equal(bits(p), bits(P))
+    forest.close()
+
+
+def test_seldon_model_class_contract(ccfd):
+    pkg, model = ccfd
+    raw, X, P, _ = load_golden("small_hard")
+    m = model.CcfdForestModel(_fa(raw), session_max_batch=256)
+    names = pkg.synth.FEATURE_NAMES if hasattr(pkg, "synth") else None
+    # wrapper passes names positionally; small request -> CUDA-graph session, large -> bulk path
+    assert np.array_equal(bits(m.predict(X[:7], names)), bits(P[:7]))
+    assert np.array_equal(bits(m.predict(X, names)), bits(P))
+    assert np.array_equal(bits(m.predict(X[:256].astype(np.float64).tolist(), [])), bits(P[:256]))
+    assert np.array_equal(bits(m.predict(np.asfortranarray(X[:100]))), bits(P[:100]))
+    assert np.array_equal(bits(m.predict(X[:200:2])), bits(P[:200:2]))
+    out = m.predict(X[:3])
+    assert out.shape == (3, 2) and out.dtype == np.float64
+    assert np.array_equal(m.decide(X), P[:, 1] > 0.5)
+    keys = {g["key"] for g in m.metrics()}
+    assert keys == {"proba_1", "Amount", "V17", "V10"}  # reference deploy/grafana/ModelPrediction.json:96-322
+    for bad in (X[0], X[:0], X[:, :29], np.where(np.arange(30) == 3, np.inf, X[:2]),
+                np.where(np.arange(30) == 3, 1e39, X[:2].astype(np.float64))):
+        with pytest.raises(ValueError):
+            m.predict(bad)
+    m.close()
+
+
+def test_session_slots_and_buckets(ccfd):
+    _, model = ccfd
+    raw, X, P, _ = load_golden("small_hard")
+    forest = model.Forest(_fa(raw))
+    s = model.Session(forest, max_batch=1024, n_slots=3)
+    for i, n in enumerate([1, 5, 31, 32, 33, 64, 65, 500, 1000, 1024, 3, 1024]):
+        assert np.array_equal(bits(s.score(i % 3, X[:n])), bits(P[:n])), n
+    # overlapped slots
+    for k in range(3):
+        s.x[k][:400] = X[k * 400: (k + 1) * 400]
+        s.submit(k, 400)
+    for k in range(3):
+        s.wait(k)
+        assert np.array_equal(bits(s.p[k][:400]), bits(P[k * 400: (k + 1) * 400]))
+    with pytest.raises(ValueError):
+        s.submit(0, 1025)
+    from ccfd_demo_summit_b200 import _lib
+    with pytest.raises(_lib.CcfdError):
+        s.wait(0)  # nothing in flight
+    s.close()
+    forest.close()
+
+
+def test_nan_rows_follow_missing_go_to_left_in_large_batches(ccfd):
+    _, model = ccfd
+    from oracle import rf_oracle
+
+    raw, X, P, _ = load_golden("nan_trained")
+    forest = model.Forest(_fa(raw))
+    rng = np.random.default_rng(3)
+    big = np.tile(X, (40, 1))  # 40k rows, NaN only in some 512-row batches after shuffling a clean half
+    clean = np.nan_to_num(big[: len(big) // 2], nan=0.25)
+    big = np.concatenate([clean, big[len(big) // 2:]])
+    rng.shuffle(big[len(big) // 2:])
+    ref = rf_oracle.predict_proba_c(raw, big)
+    for kernel in ("stream", "global"):
+        assert np.array_equal(bits(_score_device(forest, big, kernel)), bits(ref)), kernel
+    forest.close()
+
+
+# ------------------------------------------------------------------ full-size forest (configs 1-4)
+@pytest.fixture(scope="module")
+def full_forest(ccfd):
+    from ccfd_demo_summit_b200 import converter, synth
+
+    _, model = ccfd
+    X, y = synth.make_dataset(seed=1, labels="hard")
+    rf = synth.fit_forest(X, y, n_estimators=100, max_depth=10, random_state=0)
+    rf.n_jobs = 1
+    return X, rf, model.Forest(converter.from_sklearn(rf))
+
+
+def test_G1_full_batch_bitwise_vs_sklearn_on_this_box(full_forest):
+    X, rf, forest = full_forest
+    P = rf.predict_proba(X)  # n_jobs=1: the bit-reproducible order (SK/ensemble/_forest.py:704-717)
+    with open(os.path.join(GOLDEN_DIR, "g_full_hashes.json")) as fh:
+        g = json.load(fh)["G1_hard"]
+    assert hashlib.sha256(X.tobytes()).hexdigest() == g["X_sha256"]
+    assert hashlib.sha256(np.ascontiguousarray(P).tobytes()).hexdigest() == g["P_sha256"], "sklearn on this box differs from the committed golden"
+    for kernel in ("stream", "global"):
+        got = _score_device(forest, X, kernel)
+        assert np.array_equal(bits(got), bits(P)), kernel
+    got = forest.predict_proba(X)  # host pointers, chunked
+    assert np.array_equal(bits(got), bits(P))
+    assert int((got[:, 1] > 0.5).sum()) == g["fraud_at_0.5"]
+    got = _score_device(forest, X[:5000], "split")
+    assert np.array_equal(bits(got), bits(P[:5000]))
+
+
+def test_large_batch_properties(full_forest):
+    from ccfd_demo_summit_b200 import synth
+
+    X, rf, forest = full_forest
+    n = 3_000_000
+    big = synth.tile_rows(X, n)
+    xs = torch.from_numpy(big).cuda()
+    out_s = torch.empty((n, 2), dtype=torch.float64, device="cuda")
+    out_g = torch.empty((n, 2), dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    forest.predict_proba_device(xs.data_ptr(), n, 30, out_s.data_ptr(), st, "stream")
+    forest.predict_proba_device(xs.data_ptr(), n, 30, out_g.data_ptr(), st, "global")
+    assert torch.equal(out_s.view(torch.int64), out_g.view(torch.int64))  # two kernels, same bits
+    assert float((out_s.sum(dim=1) - 1).abs().max()) <= 1e-12
+    # permutation invariance: rows are independent
+    perm = torch.randperm(n, device="cuda", generator=torch.Generator(device="cuda").manual_seed(0))
+    out_p = torch.empty_like(out_s)
+    xp = xs[perm].contiguous()
+    forest.predict_proba_device(xp.data_ptr(), n, 30, out_p.data_ptr(), st, "stream")
+    assert torch.equal(out_p.view(torch.int64), out_s[perm].view(torch.int64))
+    # spot-check a slice against sklearn
+    sl = slice(1_234_567, 1_234_567 + 20_000)
+    assert np.array_equal(bits(out_s[sl].cpu().numpy()), bits(rf.predict_proba(big[sl])))
+    # decisions-only epilogue on the same rows
+    dec = torch.empty(n, dtype=torch.uint8, device="cuda")
+    forest.decide_device(xs.data_ptr(), n, 30, dec.data_ptr(), 0, 0.5, False, st, "stream")
+    assert torch.equal(dec.bool(), out_s[:, 1] > 0.5)
