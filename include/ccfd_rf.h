@@ -124,6 +124,25 @@ CCFD_API int ccfd_predict_proba(ccfd_forest* forest, const float* X, int64_t n, 
 CCFD_API int ccfd_predict_decision(ccfd_forest* forest, const float* X, int64_t n, int64_t ld, double* out,
                           uint8_t* decision, double threshold, int ge, uint32_t flags, void* stream);
 
+/* Scoring for callers that must not allocate.  No counterpart in the reference or in
+ * scikit-learn: it exists for hosts where the other entry points' cudaMallocAsync / cudaMalloc
+ * is off limits — all device memory already belongs to another allocator, or an allocation's
+ * device-wide synchronisation on the request thread is unacceptable.  Same results as
+ * ccfd_predict_proba with CCFD_DEVICE_PTRS | CCFD_KERNEL_SPLIT, but the per-(tree,row) scratch is
+ * a fixed 16 MiB array inside the library image (resident on every GPU that loads the library,
+ * until exit), so the call performs no allocation of any kind.
+ *   X, out   device pointers on the forest's device; the call returns when `out` is complete.
+ *   limit    n * n_trees <= CCFD_NOALLOC_MAX_TREE_ROWS, else CCFD_EINVAL (e.g. 10,485 rows of the
+ *            100-tree model); forests whose trees do not fit shared memory: CCFD_EUNSUPPORTED.
+ *   sharing  one scratch per GPU, shared by all calls and left as the last call wrote it.  No
+ *            clearing is needed (each call writes every slot it later reads), but calls that
+ *            overlap on one GPU race on it: issue them one after another.
+ *   set-up   the first call on each GPU resolves the array's device address and caches it; make
+ *            that call at start-up, before any CUDA stream capture. */
+#define CCFD_NOALLOC_MAX_TREE_ROWS (1 << 20)
+CCFD_API int ccfd_predict_proba_noalloc(ccfd_forest* forest, const float* X, int64_t n, int64_t ld, double* out,
+                                        void* stream);
+
 /* Latency path: `n_slots` pinned host slots of `max_batch` rows, each with its
  * own device buffers and a pre-captured CUDA graph (copy in, score, copy out).
  * Replaces the per-request work of the Seldon wrapper around predict()
