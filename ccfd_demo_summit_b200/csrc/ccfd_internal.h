@@ -41,13 +41,26 @@ struct TreeRec {
 };
 static_assert(sizeof(TreeRec) == 16, "TreeRec must be 16 bytes");
 
+// Consecutive trees whose blobs fit one shared-memory stage together: one bulk copy per group.
+struct GroupRec {
+    uint32_t first_tree;
+    uint32_t n_trees;
+    uint32_t blob_off16;   // of the first tree
+    uint32_t bytes;        // sum of the group's blob_bytes (blobs are contiguous)
+};
+static_assert(sizeof(GroupRec) == 16, "GroupRec must be 16 bytes");
+
 struct ForestDev {
     const uint8_t* blob;     // all tree blobs back to back, 16-byte aligned each
     const TreeRec* trees;    // [n_trees]
+    const GroupRec* groups;  // [n_groups] STREAM kernel's unit of transfer (null if trees do not fit)
     int32_t n_trees;
     int32_t n_features;
+    int32_t n_groups;
     uint32_t max_tree_bytes; // largest blob
     uint32_t max_depth;
+    uint32_t stage_bytes;    // STREAM ring stage: >= largest blob and >= 128 rows of features
+    uint32_t chunk_rows;     // rows of a row chunk that fit a stage, multiple of 32
 };
 
 struct ccfd_forest {

@@ -244,6 +244,7 @@ extern "C" int ccfd_forest_destroy(ccfd_forest* f) {
     }
     cudaFree((void*)f->dev.blob);
     cudaFree((void*)f->dev.trees);
+    cudaFree((void*)f->dev.groups);
     delete f;
     return CCFD_OK;
 }

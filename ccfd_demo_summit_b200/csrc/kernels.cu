@@ -5,8 +5,9 @@
 //
 // Mapping, common to the three kernels: one lane = one row, so a row's float64 sum runs over
 // trees 0..T-1 in order inside one thread exactly as scikit-learn's n_jobs=1 loop does, and
-// results are bit-identical.  Rows live in shared memory transposed ([feature][row], row stride
-// odd) so that the data-dependent `x[feature]` fetch of 32 lanes always hits 32 different banks.
+// results are bit-identical.  Rows live in shared memory transposed ([feature][row], row stride a
+// multiple of 32) so that the data-dependent `x[feature]` fetch of 32 lanes always hits 32
+// different banks.
 //
 //   STREAM  throughput.  A persistent CTA keeps 512*SPT rows resident and streams the whole forest
 //           through a shared-memory ring with 1-D TMA bulk copies (cp.async.bulk + mbarrier
@@ -15,6 +16,8 @@
 //           chip; per-(tree,row) leaf values go to scratch and a second kernel adds them in tree
 //           order.
 //   GLOBAL  forests whose trees do not fit a shared-memory stage: nodes come from L2/HBM.
+#include <algorithm>
+
 #include "ccfd_internal.h"
 
 namespace {
@@ -86,13 +89,16 @@ __device__ __forceinline__ float4 ld_stream4(const float4* p) {
 }
 
 // --------------------------------------------------------------------- row tile -> shared memory
-// Copies `rows` rows starting at src into xs[feature * XS + row] (transposed) with coalesced
+// Copies `rows` rows starting at src into xs[feature * S + row] (transposed) with coalesced
 // reads, zero-fills rows [rows, S) so the descent of idle lanes stays on finite values, and
-// reports whether this thread saw a NaN.  XS is odd (== 1 mod 32): the transposed stores of one
-// warp spread over the banks, and the descent's reads (lane == row) are conflict-free.
+// reports whether this thread saw a NaN.  The row stride S is a multiple of 32 on purpose: the
+// bank of xs[f][row] is row % 32 whatever f is, so the descent's data-dependent reads (lane ==
+// row, a different f per lane) never conflict.  The price is bank conflicts on these transposed
+// stores, paid once per row instead of once per node visit; the STREAM kernel's main path avoids
+// even that (see transpose_group).
 template <int NT, int S>
 __device__ __forceinline__ bool load_tile(float* xs, const float* __restrict__ src, int rows, int64_t ld, int F, bool vec_ok, int tid) {
-    constexpr int XS = S + 1;
+    constexpr int XS = S;
     bool nan = false;
     const int total = rows * F;
     if (vec_ok) {
@@ -169,20 +175,54 @@ __device__ __forceinline__ void descend_smem(const uint2* __restrict__ nodes, co
 }
 
 // =============================================================================== STREAM kernel
-// smem: [0,128) mbarriers | xs (F+1 rows of XS floats, last row = zeros) | ring of tree stages
+// smem: [0,128) mbarriers | xs (F+1 rows of S floats, last row = zeros) | ring of stages.
+// The ring carries everything the consumers need, in order, batch after batch:
+//   row chunks  (main path) the batch's rows, row-major, R rows per stage, straight from HBM by TMA;
+//               each consumer warp transposes the 32-row groups it owns into xs and releases the stage
+//   tree groups consecutive tree blobs that fit one stage (one bulk copy per group)
+// so the main path has no block-wide barrier and no register-staged global load at all.
+
+// One warp moves 32 rows (lane = row) from a row-major chunk in shared memory into its own columns
+// of xs.  Row stride F floats: with 8-byte loads the 16 lanes of a half-warp hit 16 different bank
+// pairs (15*r mod 16 is a permutation), and the transposed stores are lane-consecutive.
+template <int XS>
+__device__ __forceinline__ bool transpose_group(float* __restrict__ xcol, const float* __restrict__ rows_rm, int F, int lane) {
+    bool nan = false;
+    const float* rp = rows_rm + lane * F;
+    if ((F & 1) == 0) {
+        const float2* rp2 = reinterpret_cast<const float2*>(rp);
+#pragma unroll 5
+        for (int c2 = 0; c2 < (F >> 1); ++c2) {
+            const float2 v = rp2[c2];
+            xcol[(2 * c2) * XS] = v.x;
+            xcol[(2 * c2 + 1) * XS] = v.y;
+            nan |= (v.x != v.x) | (v.y != v.y);
+        }
+    } else {
+        for (int c = 0; c < F; ++c) {
+            const float v = rp[c];
+            xcol[c * XS] = v;
+            nan |= (v != v);
+        }
+    }
+    return nan;
+}
+
 template <int SPT>
-__global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const uint32_t stage_bytes, const int vec_ok) {
+__global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec_ok) {
     constexpr int S = kConsumerThreads * SPT;
-    constexpr int XS = S + 1;
+    constexpr int XS = S;
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + kMaxStages;
     float* xs = reinterpret_cast<float*>(smem + 128);
     const int F = f.n_features;
-    const int T = f.n_trees;
+    const uint32_t stage_bytes = f.stage_bytes;
     uint8_t* ring = smem + 128 + round_up((uint32_t)(F + 1) * XS * 4u, 128u);
     const int tid = threadIdx.x;
     const int64_t n_batches = (a.n + S - 1) / S;
+    const int R = (int)f.chunk_rows;          // rows per row chunk, a multiple of 32
+    const int n_chunks = (S + R - 1) / R;
 
     if (tid == 0) {
         for (int s = 0; s < n_stages; ++s) {
@@ -195,19 +235,32 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
     __syncthreads();
 
     if (tid >= kConsumerThreads) {
-        // ---- producer warp: one lane streams tree blobs, forest after forest, batch after batch
+        // ---- producer warp: one lane issues every bulk copy of this CTA
         if (tid == kConsumerThreads) {
-            int64_t my_batches = 0;
-            if ((int64_t)blockIdx.x < n_batches) my_batches = (n_batches - blockIdx.x + gridDim.x - 1) / gridDim.x;
             int stage = 0;
             uint32_t phase = 0;
-            for (int64_t b = 0; b < my_batches; ++b) {
-                for (int t = 0; t < T; ++t) {
-                    const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));  // TreeRec
-                    const uint32_t blob_off16 = (uint32_t)raw.x, blob_bytes = (uint32_t)raw.y;
+            for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+                const int64_t row0 = b * S;
+                const bool fast = vec_ok && (a.n - row0 >= (int64_t)S);
+                if (fast) {
+                    for (int c = 0; c < n_chunks; ++c) {
+                        const int r_lo = c * R;
+                        const int r_n = (S - r_lo) < R ? (S - r_lo) : R;
+                        const uint32_t bytes = (uint32_t)r_n * (uint32_t)F * 4u;
+                        mbar_wait(empty + stage, phase ^ 1u);
+                        mbar_expect_tx(full + stage, bytes);
+                        bulk_g2s(ring + (size_t)stage * stage_bytes, a.X + (row0 + r_lo) * (int64_t)F, bytes, full + stage);
+                        if (++stage == n_stages) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                }
+                for (int g = 0; g < f.n_groups; ++g) {
+                    const int4 gr = __ldg(reinterpret_cast<const int4*>(f.groups + g));  // GroupRec
                     mbar_wait(empty + stage, phase ^ 1u);
-                    mbar_expect_tx(full + stage, blob_bytes);
-                    bulk_g2s(ring + (size_t)stage * stage_bytes, f.blob + (size_t)blob_off16 * 16u, blob_bytes, full + stage);
+                    mbar_expect_tx(full + stage, (uint32_t)gr.w);
+                    bulk_g2s(ring + (size_t)stage * stage_bytes, f.blob + (size_t)(uint32_t)gr.z * 16u, (uint32_t)gr.w, full + stage);
                     if (++stage == n_stages) {
                         stage = 0;
                         phase ^= 1u;
@@ -219,37 +272,64 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
     }
 
     // ---- consumers
-    const int lane = tid & 31;
-    const double Td = (double)T;
+    const int lane = tid & 31, warp = tid >> 5;
+    const double Td = (double)f.n_trees;
     int stage = 0;
     uint32_t phase = 0;
     for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
         const int64_t row0 = b * S;
         const int rows = (int)((a.n - row0) < (int64_t)S ? (a.n - row0) : (int64_t)S);
-        named_bar_sync(1, kConsumerThreads);  // previous batch fully consumed before xs is rewritten
-        const bool my_nan = load_tile<kConsumerThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
-        const bool any_nan = named_bar_or(2, kConsumerThreads, my_nan);
+        bool any_nan;
+        if (vec_ok && rows == S) {
+            // main path: each warp lifts the 32-row groups it owns out of the row chunks
+            bool my_nan = false;
+            const int k = R >> 5;  // groups per chunk
+            for (int c = 0; c < n_chunks; ++c) {
+                const int cnt = (((S - c * R) < R ? (S - c * R) : R)) >> 5;
+                mbar_wait(full + stage, phase);
+                const float* chunk = reinterpret_cast<const float*>(ring + (size_t)stage * stage_bytes);
+                for (int lg = (warp - c * k) & (kConsumerWarps - 1); lg < cnt; lg += kConsumerWarps) {
+                    const int i = (c * k + lg) / kConsumerWarps;  // which of this thread's SPT rows
+                    my_nan |= transpose_group<XS>(xs + tid + i * kConsumerThreads, chunk + (size_t)lg * 32 * F, F, lane);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty + stage);
+                if (++stage == n_stages) {
+                    stage = 0;
+                    phase ^= 1u;
+                }
+            }
+            any_nan = __any_sync(0xffffffffu, my_nan);  // a warp only ever reads its own rows
+        } else {
+            // ragged last batch, strided or unaligned rows: cooperative load with block barriers
+            named_bar_sync(1, kConsumerThreads);
+            const bool my_nan = load_tile<kConsumerThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+            any_nan = named_bar_or(2, kConsumerThreads, my_nan);
+        }
 
         double acc0[SPT], acc1[SPT];
 #pragma unroll
         for (int i = 0; i < SPT; ++i) acc0[i] = acc1[i] = 0.0;
 
-        for (int t = 0; t < T; ++t) {
-            const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
-            const uint32_t values_off = (uint32_t)raw.z, depth = (uint32_t)raw.w;
+        for (int g = 0; g < f.n_groups; ++g) {
+            const int4 gr = __ldg(reinterpret_cast<const int4*>(f.groups + g));
             mbar_wait(full + stage, phase);
-            const uint8_t* tb = ring + (size_t)stage * stage_bytes;
-            uint32_t vidx[SPT];
-            if (!any_nan)
-                descend_smem<SPT, kConsumerThreads, false>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, (int)depth, vidx);
-            else
-                descend_smem<SPT, kConsumerThreads, true>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, (int)depth, vidx);
-            const double2* vals = reinterpret_cast<const double2*>(tb + values_off);
+            const uint8_t* gb = ring + (size_t)stage * stage_bytes;
+            for (int t = gr.x; t < gr.x + gr.y; ++t) {
+                const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
+                const uint8_t* tb = gb + (size_t)((uint32_t)raw.x - (uint32_t)gr.z) * 16u;
+                uint32_t vidx[SPT];
+                if (!any_nan)
+                    descend_smem<SPT, kConsumerThreads, false>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, raw.w, vidx);
+                else
+                    descend_smem<SPT, kConsumerThreads, true>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, raw.w, vidx);
+                const double2* vals = reinterpret_cast<const double2*>(tb + (uint32_t)raw.z);
 #pragma unroll
-            for (int i = 0; i < SPT; ++i) {
-                const double2 v = vals[vidx[i]];
-                acc0[i] += v.x;  // tree order, plain adds: SK/ensemble/_forest.py:714
-                acc1[i] += v.y;
+                for (int i = 0; i < SPT; ++i) {
+                    const double2 v = vals[vidx[i]];
+                    acc0[i] += v.x;  // tree order, plain adds: SK/ensemble/_forest.py:714
+                    acc1[i] += v.y;
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty + stage);
@@ -285,7 +365,7 @@ __device__ __forceinline__ uint32_t descend_global(const uint2* __restrict__ nod
 }
 
 __global__ void __launch_bounds__(kTileThreads) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
-    constexpr int S = kTileThreads, XS = S + 1;
+    constexpr int S = kTileThreads, XS = S;
     extern __shared__ __align__(128) uint8_t smem[];
     float* xs = reinterpret_cast<float*>(smem);
     const int F = f.n_features, T = f.n_trees, tid = threadIdx.x;
@@ -318,7 +398,7 @@ __global__ void __launch_bounds__(kTileThreads) k_global(const ForestDev f, cons
 // grid.x = 256-row tiles, grid.y = tree chunks.  Each CTA brings its chunk's trees into a 2-stage
 // shared-memory ring by TMA and writes scratch[t][row] = (v0, v1) of the leaf row lands in.
 __global__ void __launch_bounds__(kTileThreads) k_split_descend(const ForestDev f, const ScoreArgs a, double2* __restrict__ scratch, const int trees_per_cta, const uint32_t stage_bytes, const int vec_ok) {
-    constexpr int S = kTileThreads, XS = S + 1;
+    constexpr int S = kTileThreads, XS = S;
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     float* xs = reinterpret_cast<float*>(smem + 128);
@@ -410,8 +490,8 @@ struct StreamPlan {
 StreamPlan plan_stream(const ccfd_forest* f, int spt) {
     StreamPlan p;
     const uint32_t S = kConsumerThreads * spt;
-    const uint32_t xs_bytes = round_up((uint32_t)(f->dev.n_features + 1) * (S + 1) * 4u, 128u);
-    p.stage_bytes = round_up(f->dev.max_tree_bytes, 128u);
+    const uint32_t xs_bytes = round_up((uint32_t)(f->dev.n_features + 1) * S * 4u, 128u);
+    p.stage_bytes = f->dev.stage_bytes;
     const int64_t budget = (int64_t)f->smem_optin - 128 - (int64_t)xs_bytes;
     if (budget < 2 * (int64_t)p.stage_bytes) return p;
     p.n_stages = (int)(budget / p.stage_bytes);
@@ -421,7 +501,7 @@ StreamPlan plan_stream(const ccfd_forest* f, int spt) {
     return p;
 }
 
-uint32_t tile_xs_bytes(const ccfd_forest* f) { return round_up((uint32_t)(f->dev.n_features + 1) * (kTileThreads + 1) * 4u, 128u); }
+uint32_t tile_xs_bytes(const ccfd_forest* f) { return round_up((uint32_t)(f->dev.n_features + 1) * kTileThreads * 4u, 128u); }
 
 bool split_ok(const ccfd_forest* f, uint32_t* smem_bytes) {
     const uint32_t stage = round_up(f->dev.max_tree_bytes, 128u);
@@ -444,7 +524,33 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_CUDA(cudaFuncSetAttribute(k_stream<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_CUDA(cudaFuncSetAttribute(k_split_descend, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_CUDA(cudaFuncSetAttribute(k_global, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+
+    // STREAM ring geometry: a stage holds the largest tree and at least 128 rows of features.
+    const uint32_t F = (uint32_t)f->dev.n_features;
+    f->dev.stage_bytes = std::max(round_up(f->dev.max_tree_bytes, 128u), round_up(128u * F * 4u, 128u));
+    f->dev.chunk_rows = f->dev.stage_bytes / (F * 4u) / 32u * 32u;
+    f->dev.groups = nullptr;
+    f->dev.n_groups = 0;
     f->info.stream_kernel_ok = (plan_stream(f, 1).ok && split_ok(f, nullptr)) ? 1 : 0;
+    if (f->info.stream_kernel_ok) {
+        std::vector<GroupRec> groups;
+        for (int t = 0; t < f->dev.n_trees; ++t) {
+            const TreeRec& tr = f->host_trees[(size_t)t];
+            if (groups.empty() || groups.back().bytes + tr.blob_bytes > f->dev.stage_bytes)
+                groups.push_back(GroupRec{(uint32_t)t, 0u, tr.blob_off16, 0u});
+            groups.back().n_trees += 1;
+            groups.back().bytes += tr.blob_bytes;
+        }
+        GroupRec* dg = nullptr;
+        CCFD_CUDA(cudaMalloc(&dg, sizeof(GroupRec) * groups.size()));
+        cudaError_t e = cudaMemcpy(dg, groups.data(), sizeof(GroupRec) * groups.size(), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            cudaFree(dg);
+            return ccfd_cuda_fail(e, "group table upload");
+        }
+        f->dev.groups = dg;
+        f->dev.n_groups = (int32_t)groups.size();
+    }
     return CCFD_OK;
 }
 
@@ -463,8 +569,9 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
     if (kernel == CCFD_KERNEL_AUTO) kernel = ccfd_pick_kernel(f, a.n);
 
     if (kernel == CCFD_KERNEL_STREAM) {
-        // two rows per thread once there is enough work to fill the chip twice over
-        int spt = (a.n >= (int64_t)f->sm_count * kConsumerThreads * 4) ? 2 : 1;
+        // two rows per thread (1,024 resident rows per CTA) as soon as 512-row batches would need
+        // a second wave: a 1,024-row batch costs ~1.2x a 512-row one, not 2x (more chains in flight)
+        int spt = (a.n > (int64_t)f->sm_count * kConsumerThreads) ? 2 : 1;
         StreamPlan p = plan_stream(f, spt);
         if (!p.ok && spt == 2) p = plan_stream(f, spt = 1);
         if (!p.ok) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the STREAM kernel", f->dev.max_tree_bytes);
@@ -473,9 +580,9 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         const int grid = (int)(n_batches < f->sm_count ? n_batches : f->sm_count);
         // the 16-byte alignment of each batch's first row holds because S * F * 4 is a multiple of 16
         if (spt == 2)
-            k_stream<2><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, p.stage_bytes, vec_ok);
+            k_stream<2><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok);
         else
-            k_stream<1><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, p.stage_bytes, vec_ok);
+            k_stream<1><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok);
     } else if (kernel == CCFD_KERNEL_SPLIT) {
         uint32_t smem_bytes = 0;
         if (!split_ok(f, &smem_bytes)) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the SPLIT kernel", f->dev.max_tree_bytes);
