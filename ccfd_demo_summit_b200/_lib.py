@@ -40,7 +40,7 @@ SYMBOLS = [
     ("ccfd_last_error", c_char_p, []),
     ("ccfd_forest_create", c_int, [POINTER(ForestDesc), c_int, POINTER(c_void_p)]),
     ("ccfd_forest_destroy", c_int, [c_void_p]),
-    ("ccfd_forest_pack", c_int, [POINTER(ForestDesc), c_void_p, c_int64, c_void_p, POINTER(c_int64)]),
+    ("ccfd_forest_pack", c_int, [POINTER(ForestDesc), c_void_p, c_int64, c_void_p, c_void_p, POINTER(c_int64)]),
     ("ccfd_forest_get_info", c_int, [c_void_p, POINTER(ForestInfo)]),
     ("ccfd_predict_proba", c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_uint32, c_void_p]),
     ("ccfd_predict_decision", c_int,

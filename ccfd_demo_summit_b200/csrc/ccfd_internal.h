@@ -32,14 +32,29 @@ constexpr uint32_t kMglBit = 0x100u;
 constexpr int kChildShift = 9;
 constexpr int64_t kMaxNodesPerTree = (int64_t)1 << 23;
 
-// Per-tree record read by the kernels (16 bytes).
+// Per-tree record read by the kernels (32 bytes, two 16-byte uniform loads).
 struct TreeRec {
     uint32_t blob_off16;   // offset of the tree's blob in the forest buffer, in 16-byte units
     uint32_t blob_bytes;   // nodes + padding + leaf values, multiple of 16
     uint32_t values_off;   // byte offset of the leaf values inside the blob (multiple of 16)
     uint32_t depth;        // longest root-to-leaf path = trip count of the descent loop
+    // Breadth-first order puts the deepest level last and that level holds leaves only, with
+    // consecutive value indices: a row that ends at position p >= last_pos has value index
+    // p - last_pos + last_vidx and need not read its leaf slot at all.
+    uint32_t last_pos;
+    uint32_t last_vidx;
+    uint32_t reserved0, reserved1;
 };
-static_assert(sizeof(TreeRec) == 16, "TreeRec must be 16 bytes");
+static_assert(sizeof(TreeRec) == 32, "TreeRec must be 32 bytes");
+
+// The top three levels of a tree in a fixed "virtual complete" order (root; its two children; the
+// four grandchildren), copies of the packed nodes.  Where a node of the top is a leaf, its slot
+// repeats downwards (a leaf steps to itself).  Passed to the STREAM kernel by value so that these
+// levels are read through the constant bank instead of shared memory.
+struct TopNodes {
+    PackedNode n[7];
+};
+constexpr int kMaxTopTrees = 512;  // 512 * 56 B = 28 KB of kernel parameters
 
 // Consecutive trees whose blobs fit one shared-memory stage together: one bulk copy per group.
 struct GroupRec {
@@ -68,6 +83,7 @@ struct ccfd_forest {
     ForestDev dev{};
     ccfd_forest_info info{};
     std::vector<TreeRec> host_trees;
+    std::vector<TopNodes> host_top;
     int sm_count = 0;
     int smem_optin = 0;
     // host-pointer path: staging owned by the forest, one host call at a time

@@ -46,6 +46,9 @@ struct PackedTree {
     std::vector<PackedNode> nodes;
     std::vector<double> values;  // 2 per leaf
     uint32_t depth = 0;
+    uint32_t last_pos = 0;   // first position of the deepest level
+    uint32_t last_vidx = 0;  // value index of the leaf at last_pos
+    TopNodes top{};
 };
 
 // Breadth-first walk from the root; the two children of a node take adjacent positions.
@@ -99,6 +102,21 @@ int pack_tree(const ccfd_forest_desc* d, int t, PackedTree* out) {
         }
         out->nodes.push_back(pn);
     }
+    // deepest level: contiguous tail of the breadth-first order, leaves only
+    uint32_t lp = (uint32_t)order.size();
+    while (lp > 0 && level[lp - 1] == out->depth) --lp;
+    out->last_pos = lp;
+    memcpy(&out->last_vidx, &out->nodes[lp].thr, 4);
+    // top three levels in virtual complete order; a leaf repeats itself downwards
+    auto is_leaf = [F](const PackedNode& n) { return (n.meta & kFeatMask) == (uint32_t)F; };
+    TopNodes& tp = out->top;
+    tp.n[0] = out->nodes[0];
+    for (int parent = 0; parent < 3; ++parent) {
+        const PackedNode& pn = tp.n[parent];
+        const uint32_t c = pn.meta >> kChildShift;
+        tp.n[2 * parent + 1] = out->nodes[c];
+        tp.n[2 * parent + 2] = is_leaf(pn) ? out->nodes[c] : out->nodes[c + 1];
+    }
     return CCFD_OK;
 }
 
@@ -109,6 +127,7 @@ namespace {
 struct PackedForest {
     std::vector<uint8_t> blob;
     std::vector<TreeRec> trees;
+    std::vector<TopNodes> top;
     int64_t n_nodes = 0, n_leaves = 0;
     uint32_t max_depth = 0, max_bytes = 0;
 };
@@ -133,11 +152,13 @@ int pack_forest(const ccfd_forest_desc* d, PackedForest* pf) {
     int rc = validate_desc(d);
     if (rc != CCFD_OK) return rc;
     pf->trees.resize((size_t)d->n_trees);
+    pf->top.resize((size_t)d->n_trees);
     PackedTree pt;
     for (int t = 0; t < d->n_trees; ++t) {
         rc = pack_tree(d, t, &pt);
         if (rc != CCFD_OK) return rc;
-        const size_t node_bytes = pt.nodes.size() * sizeof(PackedNode);
+        // the deepest level's leaf slots are never read (TreeRec::last_pos), so they are not stored
+        const size_t node_bytes = (size_t)pt.last_pos * sizeof(PackedNode);
         const size_t values_off = (node_bytes + 15) & ~(size_t)15;
         const size_t bytes = values_off + pt.values.size() * sizeof(double);
         const size_t off = pf->blob.size();
@@ -150,6 +171,10 @@ int pack_forest(const ccfd_forest_desc* d, PackedForest* pf) {
         tr.blob_bytes = (uint32_t)bytes;
         tr.values_off = (uint32_t)values_off;
         tr.depth = pt.depth;
+        tr.last_pos = pt.last_pos;
+        tr.last_vidx = pt.last_vidx;
+        tr.reserved0 = tr.reserved1 = 0;
+        pf->top[(size_t)t] = pt.top;
         pf->n_nodes += (int64_t)pt.nodes.size();
         pf->n_leaves += (int64_t)pt.values.size() / 2;
         if (pt.depth > pf->max_depth) pf->max_depth = pt.depth;
@@ -160,7 +185,8 @@ int pack_forest(const ccfd_forest_desc* d, PackedForest* pf) {
 
 }  // namespace
 
-extern "C" int ccfd_forest_pack(const ccfd_forest_desc* d, void* blob, int64_t blob_capacity, uint32_t* tree_recs, int64_t* blob_bytes) {
+extern "C" int ccfd_forest_pack(const ccfd_forest_desc* d, void* blob, int64_t blob_capacity, uint32_t* tree_recs, uint32_t* top_nodes,
+                                int64_t* blob_bytes) {
     if (!blob_bytes) return ccfd_fail(CCFD_EINVAL, "null argument");
     PackedForest pf;
     int rc = pack_forest(d, &pf);
@@ -171,6 +197,7 @@ extern "C" int ccfd_forest_pack(const ccfd_forest_desc* d, void* blob, int64_t b
     if (blob_capacity < (int64_t)pf.blob.size()) return ccfd_fail(CCFD_EINVAL, "blob buffer too small (%lld < %lld)", (long long)blob_capacity, (long long)pf.blob.size());
     memcpy(blob, pf.blob.data(), pf.blob.size());
     memcpy(tree_recs, pf.trees.data(), sizeof(TreeRec) * pf.trees.size());
+    if (top_nodes) memcpy(top_nodes, pf.top.data(), sizeof(TopNodes) * pf.top.size());
     return CCFD_OK;
 }
 
@@ -189,6 +216,7 @@ extern "C" int ccfd_forest_create(const ccfd_forest_desc* d, int device, ccfd_fo
     if (!f) return ccfd_fail(CCFD_ENOMEM, "out of host memory");
     f->device = device;
     f->host_trees = pf.trees;
+    f->host_top = pf.top;
     const std::vector<uint8_t>& blob = pf.blob;
     const int64_t n_nodes = pf.n_nodes, n_leaves = pf.n_leaves;
     const uint32_t max_depth = pf.max_depth, max_bytes = pf.max_bytes;

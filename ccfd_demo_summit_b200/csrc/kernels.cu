@@ -17,6 +17,9 @@
 //           order.
 //   GLOBAL  forests whose trees do not fit a shared-memory stage: nodes come from L2/HBM.
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <type_traits>
 
 #include "ccfd_internal.h"
 
@@ -155,23 +158,85 @@ __device__ __forceinline__ uint32_t step(const uint2 nd, const float x) {
     return (nd.y >> kChildShift) + (left ? 0u : 1u);
 }
 
-// Nodes in shared memory, SPT independent rows per thread interleaved for ILP.
-template <int SPT, int STRIDE, bool NAN_AWARE>
-__device__ __forceinline__ void descend_smem(const uint2* __restrict__ nodes, const float* __restrict__ xcol, int XS, int depth, uint32_t (&vidx)[SPT]) {
-    uint2 nd[SPT];
-    const uint2 root = nodes[0];
+// What a thread needs to walk one tree whose blob sits in shared memory.
+struct TreeView {
+    const uint2* nodes;    // node slots [0, last_pos): the deepest level's leaf slots are not stored
+    const double2* vals;   // (v0, v1) per leaf
+    const uint2* top;      // seven top nodes in the constant bank (TOP kernels) or null
+    int depth;
+    uint32_t last_pos, last_vidx;
+};
+
+// NT trees x SPT rows = NT*SPT independent pointer chases per thread, interleaved so that the
+// shared-memory latency of one is covered by the others.  With TOP the first three levels come
+// from the kernel parameters (constant bank, warp-uniform loads: no shared-memory bandwidth) and
+// the level-1 / level-2 nodes are picked with selects.  Every tree runs exactly `depth` steps, so
+// a row ends on its leaf; rows that end on the deepest level (nearly all rows of a depth-limited
+// forest) get their value index from the position, the few others read their leaf slot.
+template <int SPT, int NT, int STRIDE, bool NAN_AWARE, bool TOP>
+__device__ __forceinline__ void descend(const TreeView (&tv)[NT], const float* __restrict__ xcol, int XS, uint32_t (&vidx)[NT][SPT]) {
+    uint32_t pos[NT][SPT];
+    int d0 = 0;
+    if (TOP) {
 #pragma unroll
-    for (int i = 0; i < SPT; ++i) nd[i] = root;
+        for (int k = 0; k < NT; ++k) {
+            const uint2* top = tv[k].top;
+            const uint2 t0 = top[0], t1 = top[1], t2 = top[2], t3 = top[3], t4 = top[4], t5 = top[5], t6 = top[6];
+#pragma unroll
+            for (int i = 0; i < SPT; ++i) {
+                const float* xc = xcol + i * STRIDE;
+                const bool r0 = step<NAN_AWARE>(t0, xc[(t0.y & kFeatMask) * XS]) != (t0.y >> kChildShift);
+                const uint2 a = r0 ? t2 : t1;
+                const bool r1 = step<NAN_AWARE>(a, xc[(a.y & kFeatMask) * XS]) != (a.y >> kChildShift);
+                const uint2 lo = r1 ? t4 : t3, hi = r1 ? t6 : t5;
+                const uint2 b = r0 ? hi : lo;
+                pos[k][i] = step<NAN_AWARE>(b, xc[(b.y & kFeatMask) * XS]);
+            }
+        }
+        d0 = 3;
+    } else {
+#pragma unroll
+        for (int k = 0; k < NT; ++k)
+#pragma unroll
+            for (int i = 0; i < SPT; ++i) pos[k][i] = 0u;
+    }
+    int dmin = tv[0].depth, dmax = tv[0].depth;
+#pragma unroll
+    for (int k = 1; k < NT; ++k) {
+        dmin = min(dmin, tv[k].depth);
+        dmax = max(dmax, tv[k].depth);
+    }
 #pragma unroll 2
-    for (int d = 0; d < depth; ++d) {
+    for (int d = d0; d < dmin; ++d) {
 #pragma unroll
-        for (int i = 0; i < SPT; ++i) {
-            const float x = xcol[(nd[i].y & kFeatMask) * XS + i * STRIDE];
-            nd[i] = nodes[step<NAN_AWARE>(nd[i], x)];
+        for (int k = 0; k < NT; ++k)
+#pragma unroll
+            for (int i = 0; i < SPT; ++i) {
+                const uint2 nd = tv[k].nodes[pos[k][i]];
+                pos[k][i] = step<NAN_AWARE>(nd, xcol[(nd.y & kFeatMask) * XS + i * STRIDE]);
+            }
+    }
+    if (NT > 1) {
+        for (int d = max(d0, dmin); d < dmax; ++d) {  // the deeper tree of the pair finishes alone
+#pragma unroll
+            for (int k = 0; k < NT; ++k)
+                if (d < tv[k].depth) {
+#pragma unroll
+                    for (int i = 0; i < SPT; ++i) {
+                        const uint2 nd = tv[k].nodes[pos[k][i]];
+                        pos[k][i] = step<NAN_AWARE>(nd, xcol[(nd.y & kFeatMask) * XS + i * STRIDE]);
+                    }
+                }
         }
     }
 #pragma unroll
-    for (int i = 0; i < SPT; ++i) vidx[i] = nd[i].x;
+    for (int k = 0; k < NT; ++k)
+#pragma unroll
+        for (int i = 0; i < SPT; ++i) {
+            uint32_t v = pos[k][i] - tv[k].last_pos + tv[k].last_vidx;
+            if (pos[k][i] < tv[k].last_pos) v = tv[k].nodes[pos[k][i]].x;
+            vidx[k][i] = v;
+        }
 }
 
 // =============================================================================== STREAM kernel
@@ -208,8 +273,26 @@ __device__ __forceinline__ bool transpose_group(float* __restrict__ xcol, const 
     return nan;
 }
 
-template <int SPT>
-__global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec_ok) {
+struct TopTable {
+    TopNodes t[kMaxTopTrees];
+};
+struct NoTop {};
+
+// Position of a consumer warp (or of the producer) in the ring.
+struct RingCursor {
+    int stage = 0;
+    uint32_t phase = 0;
+    __device__ __forceinline__ void advance(int n_stages) {
+        if (++stage == n_stages) {
+            stage = 0;
+            phase ^= 1u;
+        }
+    }
+};
+
+template <int SPT, int TPT, bool TOP>
+__global__ void __launch_bounds__(kStreamThreads, 1)
+k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec_ok, const typename std::conditional<TOP, TopTable, NoTop>::type top) {
     constexpr int S = kConsumerThreads * SPT;
     constexpr int XS = S;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -217,11 +300,12 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
     uint64_t* empty = full + kMaxStages;
     float* xs = reinterpret_cast<float*>(smem + 128);
     const int F = f.n_features;
+    const int T = f.n_trees;
     const uint32_t stage_bytes = f.stage_bytes;
     uint8_t* ring = smem + 128 + round_up((uint32_t)(F + 1) * XS * 4u, 128u);
     const int tid = threadIdx.x;
     const int64_t n_batches = (a.n + S - 1) / S;
-    const int R = (int)f.chunk_rows;          // rows per row chunk, a multiple of 32
+    const int R = (int)f.chunk_rows;  // rows per row chunk, a multiple of 32
     const int n_chunks = (S + R - 1) / R;
 
     if (tid == 0) {
@@ -237,8 +321,7 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
     if (tid >= kConsumerThreads) {
         // ---- producer warp: one lane issues every bulk copy of this CTA
         if (tid == kConsumerThreads) {
-            int stage = 0;
-            uint32_t phase = 0;
+            RingCursor cur;
             for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
                 const int64_t row0 = b * S;
                 const bool fast = vec_ok && (a.n - row0 >= (int64_t)S);
@@ -247,24 +330,18 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
                         const int r_lo = c * R;
                         const int r_n = (S - r_lo) < R ? (S - r_lo) : R;
                         const uint32_t bytes = (uint32_t)r_n * (uint32_t)F * 4u;
-                        mbar_wait(empty + stage, phase ^ 1u);
-                        mbar_expect_tx(full + stage, bytes);
-                        bulk_g2s(ring + (size_t)stage * stage_bytes, a.X + (row0 + r_lo) * (int64_t)F, bytes, full + stage);
-                        if (++stage == n_stages) {
-                            stage = 0;
-                            phase ^= 1u;
-                        }
+                        mbar_wait(empty + cur.stage, cur.phase ^ 1u);
+                        mbar_expect_tx(full + cur.stage, bytes);
+                        bulk_g2s(ring + (size_t)cur.stage * stage_bytes, a.X + (row0 + r_lo) * (int64_t)F, bytes, full + cur.stage);
+                        cur.advance(n_stages);
                     }
                 }
                 for (int g = 0; g < f.n_groups; ++g) {
                     const int4 gr = __ldg(reinterpret_cast<const int4*>(f.groups + g));  // GroupRec
-                    mbar_wait(empty + stage, phase ^ 1u);
-                    mbar_expect_tx(full + stage, (uint32_t)gr.w);
-                    bulk_g2s(ring + (size_t)stage * stage_bytes, f.blob + (size_t)(uint32_t)gr.z * 16u, (uint32_t)gr.w, full + stage);
-                    if (++stage == n_stages) {
-                        stage = 0;
-                        phase ^= 1u;
-                    }
+                    mbar_wait(empty + cur.stage, cur.phase ^ 1u);
+                    mbar_expect_tx(full + cur.stage, (uint32_t)gr.w);
+                    bulk_g2s(ring + (size_t)cur.stage * stage_bytes, f.blob + (size_t)(uint32_t)gr.z * 16u, (uint32_t)gr.w, full + cur.stage);
+                    cur.advance(n_stages);
                 }
             }
         }
@@ -273,9 +350,8 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
 
     // ---- consumers
     const int lane = tid & 31, warp = tid >> 5;
-    const double Td = (double)f.n_trees;
-    int stage = 0;
-    uint32_t phase = 0;
+    const double Td = (double)T;
+    RingCursor acq, rel;  // next stage to wait for / oldest stage this warp still holds
     for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
         const int64_t row0 = b * S;
         const int rows = (int)((a.n - row0) < (int64_t)S ? (a.n - row0) : (int64_t)S);
@@ -286,19 +362,17 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
             const int k = R >> 5;  // groups per chunk
             for (int c = 0; c < n_chunks; ++c) {
                 const int cnt = (((S - c * R) < R ? (S - c * R) : R)) >> 5;
-                mbar_wait(full + stage, phase);
-                const float* chunk = reinterpret_cast<const float*>(ring + (size_t)stage * stage_bytes);
+                mbar_wait(full + acq.stage, acq.phase);
+                const float* chunk = reinterpret_cast<const float*>(ring + (size_t)acq.stage * stage_bytes);
                 for (int lg = (warp - c * k) & (kConsumerWarps - 1); lg < cnt; lg += kConsumerWarps) {
                     const int i = (c * k + lg) / kConsumerWarps;  // which of this thread's SPT rows
                     my_nan |= transpose_group<XS>(xs + tid + i * kConsumerThreads, chunk + (size_t)lg * 32 * F, F, lane);
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(empty + stage);
-                if (++stage == n_stages) {
-                    stage = 0;
-                    phase ^= 1u;
-                }
+                if (lane == 0) mbar_arrive(empty + acq.stage);
+                acq.advance(n_stages);
             }
+            rel = acq;
             any_nan = __any_sync(0xffffffffu, my_nan);  // a warp only ever reads its own rows
         } else {
             // ragged last batch, strided or unaligned rows: cooperative load with block barriers
@@ -311,31 +385,71 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
 #pragma unroll
         for (int i = 0; i < SPT; ++i) acc0[i] = acc1[i] = 0.0;
 
-        for (int g = 0; g < f.n_groups; ++g) {
-            const int4 gr = __ldg(reinterpret_cast<const int4*>(f.groups + g));
-            mbar_wait(full + stage, phase);
-            const uint8_t* gb = ring + (size_t)stage * stage_bytes;
-            for (int t = gr.x; t < gr.x + gr.y; ++t) {
-                const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
-                const uint8_t* tb = gb + (size_t)((uint32_t)raw.x - (uint32_t)gr.z) * 16u;
-                uint32_t vidx[SPT];
-                if (!any_nan)
-                    descend_smem<SPT, kConsumerThreads, false>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, raw.w, vidx);
-                else
-                    descend_smem<SPT, kConsumerThreads, true>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, raw.w, vidx);
-                const double2* vals = reinterpret_cast<const double2*>(tb + (uint32_t)raw.z);
+        // Trees are taken TPT at a time.  A tree's stage is waited for when its group starts and
+        // handed back once the group's last tree is done, so a pair may straddle two stages.
+        int g_acq = -1;
+        int4 gr = make_int4(0, 0, 0, 0);       // group being read from: {first_tree, n_trees, blob_off16, bytes}
+        const uint8_t* gb = nullptr;
+        for (int t0 = 0; t0 < T; t0 += TPT) {
+            TreeView tv[TPT];
+            int last_of_group[TPT];
 #pragma unroll
-                for (int i = 0; i < SPT; ++i) {
-                    const double2 v = vals[vidx[i]];
-                    acc0[i] += v.x;  // tree order, plain adds: SK/ensemble/_forest.py:714
-                    acc1[i] += v.y;
+            for (int k = 0; k < TPT; ++k) {
+                const int t = (t0 + k < T) ? (t0 + k) : (T - 1);  // odd tail: the slot repeats the last tree and is ignored
+                if (t0 + k < T && t >= gr.x + gr.y) {
+                    ++g_acq;
+                    gr = __ldg(reinterpret_cast<const int4*>(f.groups + g_acq));
+                    mbar_wait(full + acq.stage, acq.phase);
+                    gb = ring + (size_t)acq.stage * stage_bytes;
+                    acq.advance(n_stages);
+                }
+                const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));      // TreeRec, first half
+                const int4 raw2 = __ldg(reinterpret_cast<const int4*>(f.trees + t) + 1);  // second half
+                const uint8_t* tb = gb + (size_t)((uint32_t)raw.x - (uint32_t)gr.z) * 16u;
+                tv[k].nodes = reinterpret_cast<const uint2*>(tb);
+                tv[k].vals = reinterpret_cast<const double2*>(tb + (uint32_t)raw.z);
+                tv[k].top = nullptr;
+                if constexpr (TOP) tv[k].top = reinterpret_cast<const uint2*>(top.t[t].n);
+                tv[k].depth = raw.w;
+                tv[k].last_pos = (uint32_t)raw2.x;
+                tv[k].last_vidx = (uint32_t)raw2.y;
+                last_of_group[k] = (t0 + k < T) && (t == gr.x + gr.y - 1);
+            }
+            uint32_t vidx[TPT][SPT];
+            if (TPT == 1 || t0 + TPT <= T) {
+                if (!any_nan)
+                    descend<SPT, TPT, kConsumerThreads, false, TOP>(tv, xs + tid, XS, vidx);
+                else
+                    descend<SPT, TPT, kConsumerThreads, true, TOP>(tv, xs + tid, XS, vidx);
+            } else {
+                TreeView one[1] = {tv[0]};
+                uint32_t v1[1][SPT];
+                if (!any_nan)
+                    descend<SPT, 1, kConsumerThreads, false, TOP>(one, xs + tid, XS, v1);
+                else
+                    descend<SPT, 1, kConsumerThreads, true, TOP>(one, xs + tid, XS, v1);
+#pragma unroll
+                for (int i = 0; i < SPT; ++i) vidx[0][i] = v1[0][i];
+            }
+#pragma unroll
+            for (int k = 0; k < TPT; ++k) {
+                if (t0 + k < T) {
+#pragma unroll
+                    for (int i = 0; i < SPT; ++i) {
+                        const double2 v = tv[k].vals[vidx[k][i]];
+                        acc0[i] += v.x;  // tree order, plain adds: SK/ensemble/_forest.py:714
+                        acc1[i] += v.y;
+                    }
                 }
             }
+            // hand back every stage whose last tree was in this step (in ring order)
             __syncwarp();
-            if (lane == 0) mbar_arrive(empty + stage);
-            if (++stage == n_stages) {
-                stage = 0;
-                phase ^= 1u;
+#pragma unroll
+            for (int k = 0; k < TPT; ++k) {
+                if (last_of_group[k]) {
+                    if (lane == 0) mbar_arrive(empty + rel.stage);
+                    rel.advance(n_stages);
+                }
             }
         }
 #pragma unroll
@@ -352,16 +466,22 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_stream(const ForestDev f,
 
 // =============================================================================== GLOBAL kernel
 // One 256-row tile per CTA, several CTAs per SM to cover L2 latency; nodes via the read-only path.
+// Branch-free like the shared-memory descent: a row that has reached the deepest level (whose leaf
+// slots are not stored) is fed a synthetic self-looping leaf instead of a load.  Deep, ragged trees:
+// the warp stops as soon as all its lanes sit on leaves.
 template <bool NAN_AWARE>
-__device__ __forceinline__ uint32_t descend_global(const uint2* __restrict__ nodes, const float* __restrict__ xcol, int XS, int depth, uint32_t leaf_feat) {
-    uint2 nd = __ldg(nodes);
+__device__ __forceinline__ uint32_t descend_global(const uint2* __restrict__ nodes, const float* __restrict__ xcol, int XS, int depth, uint32_t leaf_feat,
+                                                   uint32_t last_pos, uint32_t last_vidx) {
+    uint32_t pos = 0;
     for (int d = 0; d < depth; ++d) {
-        const float x = xcol[(nd.y & kFeatMask) * XS];
-        nd = __ldg(nodes + step<NAN_AWARE>(nd, x));
-        // deep, ragged trees: stop as soon as the whole warp sits on leaves
+        uint2 nd = make_uint2(0u, (pos << kChildShift) | leaf_feat);
+        if (pos < last_pos) nd = __ldg(nodes + pos);
+        pos = step<NAN_AWARE>(nd, xcol[(nd.y & kFeatMask) * XS]);
         if ((d & 3) == 3 && __all_sync(0xffffffffu, (nd.y & kFeatMask) == leaf_feat)) break;
     }
-    return nd.x;
+    uint32_t v = pos - last_pos + last_vidx;
+    if (pos < last_pos) v = __ldg(nodes + pos).x;
+    return v;
 }
 
 __global__ void __launch_bounds__(kTileThreads) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
@@ -378,10 +498,11 @@ __global__ void __launch_bounds__(kTileThreads) k_global(const ForestDev f, cons
     double acc0 = 0.0, acc1 = 0.0;
     for (int t = 0; t < T; ++t) {
         const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
+        const int4 raw2 = __ldg(reinterpret_cast<const int4*>(f.trees + t) + 1);
         const uint8_t* tb = f.blob + (size_t)(uint32_t)raw.x * 16u;
         const uint2* nodes = reinterpret_cast<const uint2*>(tb);
-        const uint32_t vidx = any_nan ? descend_global<true>(nodes, xs + tid, XS, raw.w, (uint32_t)F)
-                                      : descend_global<false>(nodes, xs + tid, XS, raw.w, (uint32_t)F);
+        const uint32_t vidx = any_nan ? descend_global<true>(nodes, xs + tid, XS, raw.w, (uint32_t)F, raw2.x, raw2.y)
+                                      : descend_global<false>(nodes, xs + tid, XS, raw.w, (uint32_t)F, raw2.x, raw2.y);
         const double2 v = __ldg(reinterpret_cast<const double2*>(tb + (uint32_t)raw.z) + vidx);
         acc0 += v.x;
         acc1 += v.y;
@@ -427,14 +548,22 @@ __global__ void __launch_bounds__(kTileThreads) k_split_descend(const ForestDev 
     uint32_t phase = 0;
     for (int t = t_lo; t < t_hi; ++t) {
         const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
+        const int4 raw2 = __ldg(reinterpret_cast<const int4*>(f.trees + t) + 1);
         mbar_wait(full + stage, phase);
         const uint8_t* tb = ring + (size_t)stage * stage_bytes;
-        uint32_t vidx[1];
+        TreeView tv[1];
+        tv[0].nodes = reinterpret_cast<const uint2*>(tb);
+        tv[0].vals = reinterpret_cast<const double2*>(tb + (uint32_t)raw.z);
+        tv[0].top = nullptr;
+        tv[0].depth = raw.w;
+        tv[0].last_pos = (uint32_t)raw2.x;
+        tv[0].last_vidx = (uint32_t)raw2.y;
+        uint32_t vidx[1][1];
         if (!any_nan)
-            descend_smem<1, 0, false>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, raw.w, vidx);
+            descend<1, 1, 0, false, false>(tv, xs + tid, XS, vidx);
         else
-            descend_smem<1, 0, true>(reinterpret_cast<const uint2*>(tb), xs + tid, XS, raw.w, vidx);
-        const double2 v = reinterpret_cast<const double2*>(tb + (uint32_t)raw.z)[vidx[0]];
+            descend<1, 1, 0, true, false>(tv, xs + tid, XS, vidx);
+        const double2 v = tv[0].vals[vidx[0][0]];
         if (tid < rows) scratch[(int64_t)t * a.n + row0 + tid] = v;
         const int t_next = t + kSplitStages;
         if (t_next < t_hi) {
@@ -520,8 +649,14 @@ int ccfd_kernels_init(ccfd_forest* f) {
     int major = 0;
     CCFD_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, f->device));
     if (major != 10) return ccfd_fail(CCFD_EUNSUPPORTED, "libccfd_rf is built for sm_100a (B200); device %d has compute capability major %d", f->device, major);
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_CUDA(cudaFuncSetAttribute(k_split_descend, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_CUDA(cudaFuncSetAttribute(k_global, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
 
@@ -579,10 +714,28 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         const int64_t n_batches = (a.n + S - 1) / S;
         const int grid = (int)(n_batches < f->sm_count ? n_batches : f->sm_count);
         // the 16-byte alignment of each batch's first row holds because S * F * 4 is a multiple of 16
-        if (spt == 2)
-            k_stream<2><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok);
-        else
-            k_stream<1><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok);
+        // Two trees at a time doubles the independent chains per thread; it needs a ring deep enough
+        // to hold a pair and still prefetch (>= 4 single-tree stages, or stages that hold >= 2 trees).
+        int tpt = (p.n_stages >= 4 || 2 * f->dev.n_groups <= f->dev.n_trees) ? 2 : 1;
+        bool use_top = f->dev.n_trees <= kMaxTopTrees;
+        if (const char* e = getenv("CCFD_STREAM_TPT")) tpt = atoi(e) == 2 ? 2 : 1;   // tuning knobs for experiments
+        if (const char* e = getenv("CCFD_STREAM_TOP")) use_top = use_top && atoi(e) != 0;
+#define CCFD_LAUNCH_STREAM(SPT_, TPT_)                                                                                            \
+    do {                                                                                                                          \
+        if (use_top) {                                                                                                            \
+            static_assert(sizeof(TopTable) + 256 < 32764, "kernel parameter space");                                              \
+            TopTable top; /* top three levels of every tree travel as kernel parameters (constant bank) */                         \
+            memcpy(top.t, f->host_top.data(), sizeof(TopNodes) * (size_t)f->dev.n_trees);                                         \
+            k_stream<SPT_, TPT_, true><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok, top);        \
+        } else {                                                                                                                  \
+            k_stream<SPT_, TPT_, false><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok, NoTop{});   \
+        }                                                                                                                         \
+    } while (0)
+        if (spt == 2 && tpt == 2) CCFD_LAUNCH_STREAM(2, 2);
+        else if (spt == 2) CCFD_LAUNCH_STREAM(2, 1);
+        else if (tpt == 2) CCFD_LAUNCH_STREAM(1, 2);
+        else CCFD_LAUNCH_STREAM(1, 1);
+#undef CCFD_LAUNCH_STREAM
     } else if (kernel == CCFD_KERNEL_SPLIT) {
         uint32_t smem_bytes = 0;
         if (!split_ok(f, &smem_bytes)) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the SPLIT kernel", f->dev.max_tree_bytes);

@@ -91,12 +91,14 @@ CCFD_API const char* ccfd_last_error(void);
 CCFD_API int ccfd_forest_create(const ccfd_forest_desc* desc, int device, ccfd_forest** out);
 CCFD_API int ccfd_forest_destroy(ccfd_forest* forest);
 /* The same validation and re-layout without a GPU: writes the packed image the kernels read
- * (all tree blobs back to back) and 4 uint32 per tree {offset/16, bytes, leaf-value offset,
- * depth}.  Call with blob == NULL and tree_recs == NULL to learn *blob_bytes first.  Lets a
- * deployment build step (and the CPU tests) check a forest before it reaches a GPU; has no
- * counterpart in scikit-learn, whose trees are scored in their fitted layout. */
+ * (all tree blobs back to back), 8 uint32 per tree {offset/16, bytes, leaf-value offset, depth,
+ * first position of the deepest level, value index there, 0, 0} and, if top_nodes is not NULL,
+ * 14 uint32 per tree: the seven nodes of the top three levels as the STREAM kernel receives them.
+ * Call with blob == NULL and tree_recs == NULL to learn *blob_bytes first.  Lets a deployment
+ * build step (and the CPU tests) check a forest before it reaches a GPU; has no counterpart in
+ * scikit-learn, whose trees are scored in their fitted layout. */
 CCFD_API int ccfd_forest_pack(const ccfd_forest_desc* desc, void* blob, int64_t blob_capacity, uint32_t* tree_recs,
-                              int64_t* blob_bytes);
+                              uint32_t* top_nodes, int64_t* blob_bytes);
 CCFD_API int ccfd_forest_get_info(const ccfd_forest* forest, ccfd_forest_info* info);
 
 /* out[i, 0..1] = mean over trees of the leaf class fractions of row i, float64,

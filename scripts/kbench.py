@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--trees", type=int, default=100)
     ap.add_argument("--depth", type=int, default=10)
     ap.add_argument("--kernels", default="stream,global,split")
+    ap.add_argument("--no-session", action="store_true")
     args = ap.parse_args()
     t0 = time.time()
     X, y = synth.make_dataset(seed=1 if args.labels == "hard" else 0, labels=args.labels)
@@ -58,6 +59,8 @@ def main():
             gbs = (136.0 * n + forest.info["model_bytes"]) / (med * 1e-3) / 1e9
             print(json.dumps({"n": n, "kernel": kernel, "ms_med": round(med, 4), "ms_min": round(ms[0], 4),
                               "Mtx_s": round(n / med / 1e3, 1), "GBs": round(gbs, 1), "frac": round(gbs / peak, 4)}))
+    if args.no_session:
+        return
     # latency path
     s = model.Session(forest, 1024, 4)
     s.x[0][:] = X[:1024]

@@ -21,34 +21,58 @@ def pack(fa):
     L = _lib.lib()
     d, keep = _desc(fa)
     nbytes = ctypes.c_int64()
-    _lib.check(L.ccfd_forest_pack(ctypes.byref(d), None, 0, None, ctypes.byref(nbytes)))
+    _lib.check(L.ccfd_forest_pack(ctypes.byref(d), None, 0, None, None, ctypes.byref(nbytes)))
     blob = np.zeros(nbytes.value, dtype=np.uint8)
-    recs = np.zeros((fa.n_trees, 4), dtype=np.uint32)
+    recs = np.zeros((fa.n_trees, 8), dtype=np.uint32)
+    top = np.zeros((fa.n_trees, 7, 2), dtype=np.uint32)
     _lib.check(L.ccfd_forest_pack(ctypes.byref(d), blob.ctypes.data_as(ctypes.c_void_p), blob.nbytes,
-                                  recs.ctypes.data_as(ctypes.c_void_p), ctypes.byref(nbytes)))
-    return blob, recs
+                                  recs.ctypes.data_as(ctypes.c_void_p), top.ctypes.data_as(ctypes.c_void_p),
+                                  ctypes.byref(nbytes)))
+    return blob, recs, top
 
 
-def predict_proba(blob, recs, n_features, X32):
+def _step(thr_bits, meta, x):
+    with np.errstate(invalid="ignore"):
+        left = x <= thr_bits.view(np.float32)
+    left = np.where(np.isnan(x), (meta & 0x100) != 0, left)
+    return (meta >> 9).astype(np.int64) + np.where(left, 0, 1)
+
+
+def predict_proba(blob, recs, n_features, X32, top=None):
+    """top=None: every level from the node array.  top given: the first three levels from the
+    seven-node table, picked with selects, as the STREAM kernel does (descend_smem<TOP=true>)."""
     n = X32.shape[0]
     xs = np.concatenate([X32, np.zeros((n, 1), np.float32)], axis=1)  # dummy feature row = 0
     acc = np.zeros((n, 2), dtype=np.float64)
     rows = np.arange(n)
-    for off16, nbytes, values_off, depth in recs:
+    for t, (off16, nbytes, values_off, depth, last_pos, last_vidx, _r0, _r1) in enumerate(recs):
         tb = blob[int(off16) * 16: int(off16) * 16 + int(nbytes)]
         nodes = tb[: int(values_off)].view(np.uint32).reshape(-1, 2)
         vals = tb[int(values_off):].view(np.float64).reshape(-1, 2)
         thr_bits, meta = nodes[:, 0], nodes[:, 1]
-        thr = thr_bits.view(np.float32)
-        pos = np.zeros(n, dtype=np.int64)
-        for _ in range(int(depth)):
+        if top is None:
+            pos, d0 = np.zeros(n, dtype=np.int64), 0
+        else:
+            tp = top[t]
+            pick = lambda idx: (tp[idx, 0], tp[idx, 1])  # noqa: E731
+            tb0, m0 = tp[0]
+            r0 = _step(np.full(n, tb0, np.uint32), np.full(n, m0, np.uint32), xs[rows, m0 & 0xFF]) != (m0 >> 9)
+            tb1, m1 = pick(np.where(r0, 2, 1))
+            r1 = _step(tb1, m1, xs[rows, m1 & 0xFF]) != (m1 >> 9)
+            tb2, m2 = pick(3 + 2 * r0.astype(np.int64) + r1.astype(np.int64))
+            pos, d0 = _step(tb2, m2, xs[rows, m2 & 0xFF]), 3
+        last_pos = int(last_pos)
+        assert nodes.shape[0] in (last_pos, last_pos + 1), "node array = slots above the deepest level (+ pad)"
+        for _ in range(d0, int(depth)):
+            assert np.all(pos < last_pos), "a stored slot is read on every step"
             m = meta[pos]
-            x = xs[rows, m & 0xFF]
-            with np.errstate(invalid="ignore"):
-                left = x <= thr[pos]
-            left = np.where(np.isnan(x), (m & 0x100) != 0, left)
-            pos = (m >> 9).astype(np.int64) + np.where(left, 0, 1)
-        assert np.all((meta[pos] & 0xFF) == n_features), "descent did not end on a leaf"
-        acc += vals[thr_bits[pos]]
+            pos = _step(thr_bits[pos], m, xs[rows, m & 0xFF])
+        # rows on the deepest level compute their value index, the rest read their leaf slot
+        shallow = pos < last_pos
+        assert np.all((meta[pos[shallow]] & 0xFF) == n_features), "descent did not end on a leaf"
+        vidx = pos - last_pos + int(last_vidx)
+        vidx[shallow] = thr_bits[pos[shallow]]
+        assert vidx.min() >= 0 and vidx.max() < len(vals)
+        acc += vals[vidx]
     acc /= len(recs)
     return acc

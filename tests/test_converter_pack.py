@@ -40,28 +40,34 @@ def test_floored_threshold_is_equivalent_for_every_float32_neighbour():
 def test_packed_walk_matches_sklearn_bitwise(golden):
     name, raw, X, P, _ = golden
     fa = _fa(raw)
-    blob, recs = packed_emulator.pack(fa)
-    got = packed_emulator.predict_proba(blob, recs, fa.n_features, np.ascontiguousarray(X, dtype=np.float32))
+    blob, recs, top = packed_emulator.pack(fa)
+    X32 = np.ascontiguousarray(X, dtype=np.float32)
+    got = packed_emulator.predict_proba(blob, recs, fa.n_features, X32)
+    assert np.array_equal(bits(got), bits(P)), name
+    got = packed_emulator.predict_proba(blob, recs, fa.n_features, X32, top=top)  # top levels from the 7-node table
     assert np.array_equal(bits(got), bits(P)), name
 
 
 def test_pack_layout_invariants():
     raw, *_ = load_golden("bestfirst")  # best-first builder: source nodes are not in pre-order
     fa = _fa(raw)
-    blob, recs = packed_emulator.pack(fa)
+    blob, recs, _ = packed_emulator.pack(fa)
     assert blob.nbytes % 16 == 0
-    for t, (off16, nbytes, values_off, depth) in enumerate(recs):
+    for t, (off16, nbytes, values_off, depth, last_pos, last_vidx, *_rest) in enumerate(recs):
         assert nbytes % 16 == 0 and values_off % 16 == 0
         n_src = int(raw.tree_offsets[t + 1] - raw.tree_offsets[t])
         n_leaves = (int(nbytes) - int(values_off)) // 16
         assert n_leaves == (n_src + 1) // 2
-        nodes = blob[int(off16) * 16: int(off16) * 16 + n_src * 8].view(np.uint32).reshape(-1, 2)
+        # slots of the deepest level (leaves only) are not stored
+        assert int(values_off) == (int(last_pos) * 8 + 15) // 16 * 16
+        nodes = blob[int(off16) * 16: int(off16) * 16 + int(last_pos) * 8].view(np.uint32).reshape(-1, 2)
         internal = (nodes[:, 1] & 0xFF) != fa.n_features
         child = nodes[internal, 1] >> 9
         # siblings adjacent, children after parents, every slot referenced exactly once
         assert np.array_equal(np.sort(np.concatenate([child, child + 1])), np.arange(1, n_src))
         assert np.all(child > np.nonzero(internal)[0])
         assert np.array_equal(nodes[~internal, 1] >> 9, np.nonzero(~internal)[0])  # leaves point at themselves
+        assert n_src - int(last_pos) == n_leaves - int(last_vidx)  # deepest level: consecutive value indices to the end
 
 
 def test_from_sklearn_reads_a_fitted_forest():
@@ -76,9 +82,9 @@ def test_from_sklearn_reads_a_fitted_forest():
     raw = rf_oracle.extract_raw(rf)
     assert fa.n_trees == 5 and fa.n_features == 30 and fa.n_classes == 2
     assert np.array_equal(fa.tree_offsets, raw.tree_offsets)
-    blob, recs = packed_emulator.pack(fa)
+    blob, recs, top = packed_emulator.pack(fa)
     rf.n_jobs = 1
-    assert np.array_equal(bits(packed_emulator.predict_proba(blob, recs, 30, X[:500])), bits(rf.predict_proba(X[:500])))
+    assert np.array_equal(bits(packed_emulator.predict_proba(blob, recs, 30, X[:500], top)), bits(rf.predict_proba(X[:500])))
 
 
 @pytest.mark.parametrize("breakage", ["cycle", "feature", "one_child", "nan_thr", "offsets", "classes", "child_range"])
