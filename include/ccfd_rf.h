@@ -160,6 +160,19 @@ CCFD_API int ccfd_session_submit(ccfd_session* session, int32_t slot, int64_t n_
 /* Block until the slot's results are visible in its p buffer. */
 CCFD_API int ccfd_session_wait(ccfd_session* session, int32_t slot);
 
+/* Request text -> float32 rows, written straight into `dst` (typically a session slot's pinned x
+ * buffer, so the bytes the GPU copies are produced in one pass).  Replaces the JSON decoding of the
+ * Seldon Python wrapper in front of predict() for requests arriving at reference
+ * deploy/router.yaml:65-68, and the CSV handling of the Kafka consumer side of reference
+ * deploy/kafka/ProducerDeployment.yaml:88-97.  Accepts Seldon JSON ("ndarray" or "tensor"/"values"
+ * payloads; numbers before the payload key, e.g. "shape", are ignored), JSON lines, and CSV rows
+ * (header words skipped, quoted numbers accepted).  Every `cols_in` numbers form a row and the first
+ * `cols_keep` are kept (31 -> 30 drops the CSV's Class column).  Values take the same
+ * text -> float64 -> float32 roundings as json.loads + numpy.  NaN/null -> NaN, Infinity -> inf
+ * (for the caller to reject, as sklearn does).  Pure host code: no GPU is touched. */
+CCFD_API int ccfd_parse_rows(const char* text, int64_t len, int32_t cols_in, int32_t cols_keep, float* dst,
+                             int64_t cap_rows, int64_t* n_rows);
+
 #ifdef __cplusplus
 }
 #endif
