@@ -43,18 +43,34 @@ struct TreeRec {
     // p - last_pos + last_vidx and need not read its leaf slot at all.
     uint32_t last_pos;
     uint32_t last_vidx;
-    uint32_t reserved0, reserved1;
+    // filled when the forest is bound to a device (STREAM ring geometry), 0 in ccfd_forest_pack output
+    uint32_t rel_off;      // byte offset of the blob inside its tree group (= inside a ring stage)
+    uint32_t group_flags;  // bit 0: first tree of its group, bit 1: last tree of its group
 };
 static_assert(sizeof(TreeRec) == 32, "TreeRec must be 32 bytes");
 
 // The top three levels of a tree in a fixed "virtual complete" order (root; its two children; the
 // four grandchildren), copies of the packed nodes.  Where a node of the top is a leaf, its slot
-// repeats downwards (a leaf steps to itself).  Passed to the STREAM kernel by value so that these
-// levels are read through the constant bank instead of shared memory.
+// repeats downwards (a leaf steps to itself).
 struct TopNodes {
     PackedNode n[7];
 };
-constexpr int kMaxTopTrees = 512;  // 512 * 56 B = 28 KB of kernel parameters
+
+// Everything a consumer warp needs to know about a tree, passed to the STREAM kernel BY VALUE so
+// that it is read through the constant bank: warp-uniform per-tree metadata fetched with ordinary
+// loads costs a full 32-lane write-back in the same L1/shared-memory data pipe that bounds the
+// kernel, the constant bank costs nothing there.
+struct TreeParam {
+    TopNodes top;          // 56 B
+    uint32_t rel_off;      // blob offset inside its stage
+    uint32_t values_off;   // leaf values inside the blob
+    uint32_t depth_flags;  // depth | first_of_group << 16 | last_of_group << 17
+    uint32_t last_pos;
+    uint32_t last_vidx;
+    uint32_t pad;
+};
+static_assert(sizeof(TreeParam) == 80, "TreeParam must be 80 bytes");
+constexpr int kMaxParamTrees = 400;  // 400 * 80 B = 32,000 B of the 32,764 B kernel parameter space
 
 // Consecutive trees whose blobs fit one shared-memory stage together: one bulk copy per group.
 struct GroupRec {
@@ -84,6 +100,7 @@ struct ccfd_forest {
     ccfd_forest_info info{};
     std::vector<TreeRec> host_trees;
     std::vector<TopNodes> host_top;
+    std::vector<TreeParam> host_params;  // STREAM kernel parameter table (n_trees <= kMaxParamTrees)
     int sm_count = 0;
     int smem_optin = 0;
     // host-pointer path: staging owned by the forest, one host call at a time

@@ -173,7 +173,7 @@ int pack_forest(const ccfd_forest_desc* d, PackedForest* pf) {
         tr.depth = pt.depth;
         tr.last_pos = pt.last_pos;
         tr.last_vidx = pt.last_vidx;
-        tr.reserved0 = tr.reserved1 = 0;
+        tr.rel_off = tr.group_flags = 0;
         pf->top[(size_t)t] = pt.top;
         pf->n_nodes += (int64_t)pt.nodes.size();
         pf->n_leaves += (int64_t)pt.values.size() / 2;

@@ -274,7 +274,7 @@ __device__ __forceinline__ bool transpose_group(float* __restrict__ xcol, const 
 }
 
 struct TopTable {
-    TopNodes t[kMaxTopTrees];
+    TreeParam t[kMaxParamTrees];
 };
 struct NoTop {};
 
@@ -387,33 +387,43 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
 
         // Trees are taken TPT at a time.  A tree's stage is waited for when its group starts and
         // handed back once the group's last tree is done, so a pair may straddle two stages.
-        int g_acq = -1;
-        int4 gr = make_int4(0, 0, 0, 0);       // group being read from: {first_tree, n_trees, blob_off16, bytes}
         const uint8_t* gb = nullptr;
         for (int t0 = 0; t0 < T; t0 += TPT) {
             TreeView tv[TPT];
             int last_of_group[TPT];
 #pragma unroll
             for (int k = 0; k < TPT; ++k) {
-                const int t = (t0 + k < T) ? (t0 + k) : (T - 1);  // odd tail: the slot repeats the last tree and is ignored
-                if (t0 + k < T && t >= gr.x + gr.y) {
-                    ++g_acq;
-                    gr = __ldg(reinterpret_cast<const int4*>(f.groups + g_acq));
+                const bool valid = t0 + k < T;
+                const int t = valid ? (t0 + k) : (T - 1);  // odd tail: the slot repeats the last tree and is ignored
+                uint32_t rel_off, values_off, depth_flags;
+                if constexpr (TOP) {
+                    const TreeParam& tp = top.t[t];  // constant bank
+                    rel_off = tp.rel_off;
+                    values_off = tp.values_off;
+                    depth_flags = tp.depth_flags;
+                    tv[k].last_pos = tp.last_pos;
+                    tv[k].last_vidx = tp.last_vidx;
+                    tv[k].top = reinterpret_cast<const uint2*>(tp.top.n);
+                } else {
+                    const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));      // TreeRec, first half
+                    const int4 raw2 = __ldg(reinterpret_cast<const int4*>(f.trees + t) + 1);  // second half
+                    rel_off = (uint32_t)raw2.z;
+                    values_off = (uint32_t)raw.z;
+                    depth_flags = (uint32_t)raw.w | ((uint32_t)raw2.w << 16);
+                    tv[k].last_pos = (uint32_t)raw2.x;
+                    tv[k].last_vidx = (uint32_t)raw2.y;
+                    tv[k].top = nullptr;
+                }
+                if (valid && (depth_flags & 0x10000u)) {  // first tree of a group: its stage must have landed
                     mbar_wait(full + acq.stage, acq.phase);
                     gb = ring + (size_t)acq.stage * stage_bytes;
                     acq.advance(n_stages);
                 }
-                const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));      // TreeRec, first half
-                const int4 raw2 = __ldg(reinterpret_cast<const int4*>(f.trees + t) + 1);  // second half
-                const uint8_t* tb = gb + (size_t)((uint32_t)raw.x - (uint32_t)gr.z) * 16u;
+                const uint8_t* tb = gb + rel_off;
                 tv[k].nodes = reinterpret_cast<const uint2*>(tb);
-                tv[k].vals = reinterpret_cast<const double2*>(tb + (uint32_t)raw.z);
-                tv[k].top = nullptr;
-                if constexpr (TOP) tv[k].top = reinterpret_cast<const uint2*>(top.t[t].n);
-                tv[k].depth = raw.w;
-                tv[k].last_pos = (uint32_t)raw2.x;
-                tv[k].last_vidx = (uint32_t)raw2.y;
-                last_of_group[k] = (t0 + k < T) && (t == gr.x + gr.y - 1);
+                tv[k].vals = reinterpret_cast<const double2*>(tb + values_off);
+                tv[k].depth = (int)(depth_flags & 0xFFFFu);
+                last_of_group[k] = valid && (depth_flags & 0x20000u);
             }
             uint32_t vidx[TPT][SPT];
             if (TPT == 1 || t0 + TPT <= T) {
@@ -670,21 +680,43 @@ int ccfd_kernels_init(ccfd_forest* f) {
     if (f->info.stream_kernel_ok) {
         std::vector<GroupRec> groups;
         for (int t = 0; t < f->dev.n_trees; ++t) {
-            const TreeRec& tr = f->host_trees[(size_t)t];
-            if (groups.empty() || groups.back().bytes + tr.blob_bytes > f->dev.stage_bytes)
+            TreeRec& tr = f->host_trees[(size_t)t];
+            if (tr.depth > 0xFFFFu) return ccfd_fail(CCFD_EUNSUPPORTED, "tree %d is %u levels deep", t, tr.depth);
+            if (groups.empty() || groups.back().bytes + tr.blob_bytes > f->dev.stage_bytes) {
+                if (!groups.empty()) f->host_trees[(size_t)t - 1].group_flags |= 2u;
                 groups.push_back(GroupRec{(uint32_t)t, 0u, tr.blob_off16, 0u});
+                tr.group_flags |= 1u;
+            }
+            tr.rel_off = (tr.blob_off16 - groups.back().blob_off16) * 16u;
             groups.back().n_trees += 1;
             groups.back().bytes += tr.blob_bytes;
         }
+        f->host_trees.back().group_flags |= 2u;
         GroupRec* dg = nullptr;
         CCFD_CUDA(cudaMalloc(&dg, sizeof(GroupRec) * groups.size()));
         cudaError_t e = cudaMemcpy(dg, groups.data(), sizeof(GroupRec) * groups.size(), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess)  // the tree records now carry their place in the ring
+            e = cudaMemcpy((void*)f->dev.trees, f->host_trees.data(), sizeof(TreeRec) * f->host_trees.size(), cudaMemcpyHostToDevice);
         if (e != cudaSuccess) {
             cudaFree(dg);
             return ccfd_cuda_fail(e, "group table upload");
         }
         f->dev.groups = dg;
         f->dev.n_groups = (int32_t)groups.size();
+        if (f->dev.n_trees <= kMaxParamTrees) {
+            f->host_params.resize((size_t)f->dev.n_trees);
+            for (int t = 0; t < f->dev.n_trees; ++t) {
+                const TreeRec& tr = f->host_trees[(size_t)t];
+                TreeParam& tp = f->host_params[(size_t)t];
+                tp.top = f->host_top[(size_t)t];
+                tp.rel_off = tr.rel_off;
+                tp.values_off = tr.values_off;
+                tp.depth_flags = tr.depth | (tr.group_flags << 16);
+                tp.last_pos = tr.last_pos;
+                tp.last_vidx = tr.last_vidx;
+                tp.pad = 0;
+            }
+        }
     }
     return CCFD_OK;
 }
@@ -717,15 +749,15 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         // Two trees at a time doubles the independent chains per thread; it needs a ring deep enough
         // to hold a pair and still prefetch (>= 4 single-tree stages, or stages that hold >= 2 trees).
         int tpt = (p.n_stages >= 4 || 2 * f->dev.n_groups <= f->dev.n_trees) ? 2 : 1;
-        bool use_top = f->dev.n_trees <= kMaxTopTrees;
+        bool use_top = !f->host_params.empty();
         if (const char* e = getenv("CCFD_STREAM_TPT")) tpt = atoi(e) == 2 ? 2 : 1;   // tuning knobs for experiments
         if (const char* e = getenv("CCFD_STREAM_TOP")) use_top = use_top && atoi(e) != 0;
 #define CCFD_LAUNCH_STREAM(SPT_, TPT_)                                                                                            \
     do {                                                                                                                          \
         if (use_top) {                                                                                                            \
             static_assert(sizeof(TopTable) + 256 < 32764, "kernel parameter space");                                              \
-            TopTable top; /* top three levels of every tree travel as kernel parameters (constant bank) */                         \
-            memcpy(top.t, f->host_top.data(), sizeof(TopNodes) * (size_t)f->dev.n_trees);                                         \
+            TopTable top; /* per-tree metadata and top three levels travel as kernel parameters (constant bank) */                 \
+            memcpy(top.t, f->host_params.data(), sizeof(TreeParam) * f->host_params.size());                                      \
             k_stream<SPT_, TPT_, true><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok, top);        \
         } else {                                                                                                                  \
             k_stream<SPT_, TPT_, false><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok, NoTop{});   \

@@ -88,6 +88,30 @@ def test_host_pointer_path_and_oracle(ccfd, golden):
     forest.close()
 
 
+def test_many_small_trees_take_the_table_free_stream_path(ccfd):
+    """More trees than the kernel-parameter table holds (400): per-tree metadata comes from global
+    memory instead of the constant bank.  450 trees = the 'small_easy' forest repeated."""
+    from oracle import rf_oracle
+
+    _, model = ccfd
+    raw, X, _, _ = load_golden("small_easy")
+    reps = 450 // raw.n_trees + 1
+    sizes = np.diff(raw.tree_offsets)
+    offs = np.concatenate([[0], np.cumsum(np.tile(sizes, reps))])[: 451]
+    n_nodes = int(offs[-1])
+    tile = lambda a: np.concatenate([a] * reps)[:n_nodes]  # noqa: E731
+    big = rf_oracle.RawForest(offs.astype(np.int64), tile(raw.left), tile(raw.right), tile(raw.feature), tile(raw.threshold),
+                              tile(raw.missing_go_to_left), np.concatenate([raw.value] * reps)[:n_nodes], raw.n_features, raw.n_classes)
+    assert big.n_trees == 450
+    rows = np.tile(X, (40, 1))  # 40k rows -> STREAM with two rows per thread
+    want = rf_oracle.predict_proba_c(big, rows)
+    forest = model.Forest(_fa(big))
+    for kernel in ("stream", "split", "global"):
+        got = _score_device(forest, rows if kernel != "split" else rows[:3000], kernel)
+        assert np.array_equal(bits(got), bits(want[: len(got)])), kernel
+    forest.close()
+
+
 def test_fused_decision_matches_threshold_rule(ccfd):
     _, model = ccfd
     raw, X, P, _ = load_golden("deep")  # pure leaves: p is k/T, ties at the threshold really happen
@@ -192,6 +216,29 @@ def test_G1_full_batch_bitwise_vs_sklearn_on_this_box(full_forest):
     assert int((got[:, 1] > 0.5).sum()) == g["fraud_at_0.5"]
     got = _score_device(forest, X[:5000], "split")
     assert np.array_equal(bits(got), bits(P[:5000]))
+
+
+def test_G2_easy_label_forest_bitwise_vs_sklearn(ccfd):
+    """Kaggle-like forest (0.17 % positives, separable): tens of nodes per tree, trees of very
+    different depths, many trees per shared-memory stage."""
+    from ccfd_demo_summit_b200 import converter, synth
+
+    _, model = ccfd
+    X, y = synth.make_dataset(seed=0, labels="easy")
+    rf = synth.fit_forest(X, y, n_estimators=100, max_depth=10, random_state=0)
+    rf.n_jobs = 1
+    P = rf.predict_proba(X)
+    with open(os.path.join(GOLDEN_DIR, "g_full_hashes.json")) as fh:
+        g = json.load(fh)["G2_easy"]
+    assert hashlib.sha256(np.ascontiguousarray(P).tobytes()).hexdigest() == g["P_sha256"]
+    forest = model.Forest(converter.from_sklearn(rf))
+    for kernel in ("stream", "global"):
+        assert np.array_equal(bits(_score_device(forest, X, kernel)), bits(P)), kernel
+    assert np.array_equal(bits(_score_device(forest, X[:4000], "split")), bits(P[:4000]))
+    Xn = X[:50000].copy()
+    Xn[::7, 3] = np.nan
+    assert np.array_equal(bits(_score_device(forest, Xn, "stream")), bits(rf.predict_proba(Xn)))
+    forest.close()
 
 
 def test_large_batch_properties(full_forest):
