@@ -8,6 +8,7 @@
 namespace {
 
 constexpr int64_t kHostChunkRows = 1 << 20;  // 120 MB of fp32 rows per staged chunk
+constexpr int64_t kDirectOutRows = 4096;     // session buckets up to this size write results straight to pinned host memory
 
 int ensure_staging(ccfd_forest* f, int64_t rows) {
     if (f->stage_rows >= rows) return CCFD_OK;
@@ -150,9 +151,14 @@ int build_slot(ccfd_session* ss, ccfd_slot& s) {
     const ccfd_forest* f = ss->f;
     const int F = f->dev.n_features;
     const size_t xb = sizeof(float) * (size_t)ss->max_batch * F, pb = sizeof(double) * 2 * (size_t)ss->max_batch;
-    CCFD_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    // requests are short: give them the highest stream priority so they overtake bulk scoring
+    int prio_lo = 0, prio_hi = 0;
+    CCFD_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CCFD_CUDA(cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_hi));
     CCFD_CUDA(cudaHostAlloc(&s.hx, xb, cudaHostAllocDefault));
-    CCFD_CUDA(cudaHostAlloc(&s.hp, pb, cudaHostAllocDefault));
+    CCFD_CUDA(cudaHostAlloc(&s.hp, pb, cudaHostAllocMapped));
+    double* hp_dev = nullptr;  // the same pinned result buffer as the GPU sees it
+    CCFD_CUDA(cudaHostGetDevicePointer(&hp_dev, s.hp, 0));
     memset(s.hx, 0, xb);
     CCFD_CUDA(cudaMalloc(&s.dx, xb));
     CCFD_CUDA(cudaMalloc(&s.dp, pb));
@@ -161,17 +167,21 @@ int build_slot(ccfd_session* ss, ccfd_slot& s) {
         if (ccfd_pick_kernel(f, cap) == CCFD_KERNEL_SPLIT) scratch_bytes = std::max(scratch_bytes, ccfd_split_scratch_bytes(f, cap));
     if (scratch_bytes) CCFD_CUDA(cudaMalloc(&s.scratch, (size_t)scratch_bytes));
 
-    // One graph per bucket: copy in -> score -> copy out, all addresses fixed at capture.
+    // One graph per bucket: copy in -> score -> copy out, all addresses fixed at capture.  Small
+    // buckets skip the copy-out: their last kernel writes the 16 bytes per row straight into the
+    // pinned host buffer (one graph node and one DMA set-up less on the critical path).
     for (int64_t cap : ss->buckets) {
+        const bool direct_out = cap <= kDirectOutRows;
         cudaGraph_t graph = nullptr;
         CCFD_CUDA(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
         cudaError_t e = cudaMemcpyAsync(s.dx, s.hx, sizeof(float) * (size_t)cap * F, cudaMemcpyHostToDevice, s.stream);
         int rc = CCFD_OK;
         if (e == cudaSuccess) {
-            ScoreArgs a{s.dx, cap, F, s.dp, nullptr, 0.5, 0};
+            ScoreArgs a{s.dx, cap, F, direct_out ? hp_dev : s.dp, nullptr, 0.5, 0};
             rc = ccfd_launch_score(f, a, ccfd_pick_kernel(f, cap), s.scratch, s.stream);
         }
-        if (e == cudaSuccess && rc == CCFD_OK) e = cudaMemcpyAsync(s.hp, s.dp, sizeof(double) * 2 * (size_t)cap, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess && rc == CCFD_OK && !direct_out)
+            e = cudaMemcpyAsync(s.hp, s.dp, sizeof(double) * 2 * (size_t)cap, cudaMemcpyDeviceToHost, s.stream);
         cudaError_t e2 = cudaStreamEndCapture(s.stream, &graph);
         if (rc != CCFD_OK) {
             if (graph) cudaGraphDestroy(graph);

@@ -592,30 +592,39 @@ __global__ void __launch_bounds__(kTileThreads) k_split_descend(const ForestDev 
 }
 
 // out[row] = (sum over t = 0..T-1, in that order, of scratch[t][row]) / T
+// A CTA owns 32 rows.  All 128 threads first pull a [<=64 trees][32 rows] tile of scratch into
+// shared memory with independent coalesced loads (one L2 round trip instead of one per tree), then
+// the first warp adds each row's values in tree order.
+constexpr int kReduceRows = 32;
+constexpr int kReduceTrees = 64;
 __global__ void __launch_bounds__(128) k_split_reduce(const double2* __restrict__ scratch, const int T, const ScoreArgs a) {
-    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (row >= a.n) return;
+    __shared__ double2 tile[kReduceTrees][kReduceRows];
+    const int64_t row0 = (int64_t)blockIdx.x * kReduceRows;
+    const int rows = (int)((a.n - row0) < (int64_t)kReduceRows ? (a.n - row0) : (int64_t)kReduceRows);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     double acc0 = 0.0, acc1 = 0.0;
-    int t = 0;
-    for (; t + 4 <= T; t += 4) {
-        double2 v[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) v[j] = scratch[(int64_t)(t + j) * a.n + row];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            acc0 += v[j].x;
-            acc1 += v[j].y;
+    for (int t0 = 0; t0 < T; t0 += kReduceTrees) {
+        const int nt = min(kReduceTrees, T - t0);
+        if (t0) __syncthreads();
+#pragma unroll 4
+        for (int t = w; t < nt; t += 4)
+            if (lane < rows) tile[t][lane] = scratch[(int64_t)(t0 + t) * a.n + row0 + lane];
+        __syncthreads();
+        if (w == 0 && lane < rows) {
+#pragma unroll 8
+            for (int t = 0; t < nt; ++t) {
+                const double2 v = tile[t][lane];
+                acc0 += v.x;
+                acc1 += v.y;
+            }
         }
     }
-    for (; t < T; ++t) {
-        const double2 v = scratch[(int64_t)t * a.n + row];
-        acc0 += v.x;
-        acc1 += v.y;
+    if (w == 0 && lane < rows) {
+        const double Td = (double)T;
+        const double p0 = acc0 / Td, p1 = acc1 / Td;
+        if (a.out) reinterpret_cast<double2*>(a.out)[row0 + lane] = make_double2(p0, p1);
+        if (a.decision) a.decision[row0 + lane] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
     }
-    const double Td = (double)T;
-    const double p0 = acc0 / Td, p1 = acc1 / Td;
-    if (a.out) reinterpret_cast<double2*>(a.out)[row] = make_double2(p0, p1);
-    if (a.decision) a.decision[row] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
 }
 
 // ------------------------------------------------------------------------------- host helpers
@@ -784,7 +793,7 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         const uint32_t stage_bytes = round_up(f->dev.max_tree_bytes, 128u);
         dim3 grid((unsigned)tiles, (unsigned)chunks);
         k_split_descend<<<grid, kTileThreads, smem_bytes, stream>>>(f->dev, a, static_cast<double2*>(scratch), trees_per_cta, stage_bytes, vec_ok);
-        k_split_reduce<<<(unsigned)((a.n + 127) / 128), 128, 0, stream>>>(static_cast<const double2*>(scratch), f->dev.n_trees, a);
+        k_split_reduce<<<(unsigned)((a.n + kReduceRows - 1) / kReduceRows), 128, 0, stream>>>(static_cast<const double2*>(scratch), f->dev.n_trees, a);
     } else if (kernel == CCFD_KERNEL_GLOBAL) {
         const int64_t tiles = (a.n + kTileThreads - 1) / kTileThreads;
         if (tiles > 0x7FFFFFFFll) return ccfd_fail(CCFD_EINVAL, "too many rows for one launch");
