@@ -606,9 +606,14 @@ __global__ void __launch_bounds__(128) k_split_reduce(const double2* __restrict_
     for (int t0 = 0; t0 < T; t0 += kReduceTrees) {
         const int nt = min(kReduceTrees, T - t0);
         if (t0) __syncthreads();
-#pragma unroll 4
-        for (int t = w; t < nt; t += 4)
-            if (lane < rows) tile[t][lane] = scratch[(int64_t)(t0 + t) * a.n + row0 + lane];
+        double2 v[kReduceTrees / 4];  // all of this thread's loads are issued before any is used
+#pragma unroll
+        for (int j = 0; j < kReduceTrees / 4; ++j) {
+            const int t = w + 4 * j;
+            v[j] = (t < nt && lane < rows) ? scratch[(int64_t)(t0 + t) * a.n + row0 + lane] : make_double2(0.0, 0.0);
+        }
+#pragma unroll
+        for (int j = 0; j < kReduceTrees / 4; ++j) tile[w + 4 * j][lane] = v[j];
         __syncthreads();
         if (w == 0 && lane < rows) {
 #pragma unroll 8
