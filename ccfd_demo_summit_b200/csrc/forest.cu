@@ -9,6 +9,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <new>
 
 #include "ccfd_internal.h"
@@ -52,7 +53,11 @@ struct PackedTree {
 };
 
 // Breadth-first walk from the root; the two children of a node take adjacent positions.
-int pack_tree(const ccfd_forest_desc* d, int t, PackedTree* out) {
+// `big` is the layout for trees that can never sit in shared memory (the GLOBAL kernel reads them
+// from L2/HBM): equal leaf values share one table entry (an unbounded-depth forest has pure leaves
+// only, so its 16-byte-per-leaf table collapses to two entries and the forest halves), and every
+// leaf slot is kept because the value index no longer follows from the position.
+int pack_tree(const ccfd_forest_desc* d, int t, bool big, PackedTree* out) {
     const int64_t lo = d->tree_offsets[t], hi = d->tree_offsets[t + 1];
     const int64_t cnt = hi - lo;
     if (cnt < 1) return ccfd_fail(CCFD_EINVAL, "tree %d has no nodes", t);
@@ -70,17 +75,29 @@ int pack_tree(const ccfd_forest_desc* d, int t, PackedTree* out) {
     out->nodes.clear();
     out->values.clear();
     out->depth = 0;
+    std::map<std::pair<uint64_t, uint64_t>, uint32_t> seen_values;
     for (size_t pos = 0; pos < order.size(); ++pos) {
         const int64_t u = lo + order[pos];
         const int32_t l = d->left[u], r = d->right[u];
         PackedNode pn;
         if (l < 0 || r < 0) {
             if (l >= 0 || r >= 0) return ccfd_fail(CCFD_EINVAL, "tree %d node %d has exactly one child", t, order[pos]);
-            const uint32_t vidx = (uint32_t)(out->values.size() / 2);
+            uint32_t vidx = (uint32_t)(out->values.size() / 2);
             const double v0 = d->value[u * 2], v1 = d->value[u * 2 + 1];
             if (!std::isfinite(v0) || !std::isfinite(v1)) return ccfd_fail(CCFD_EINVAL, "tree %d node %d has a non-finite leaf value", t, order[pos]);
-            out->values.push_back(v0);
-            out->values.push_back(v1);
+            bool fresh = true;
+            if (big) {
+                uint64_t b0, b1;
+                memcpy(&b0, &v0, 8);
+                memcpy(&b1, &v1, 8);
+                auto ins = seen_values.emplace(std::make_pair(b0, b1), vidx);
+                fresh = ins.second;
+                vidx = ins.first->second;
+            }
+            if (fresh) {
+                out->values.push_back(v0);
+                out->values.push_back(v1);
+            }
             memcpy(&pn.thr, &vidx, 4);
             pn.meta = ((uint32_t)pos << kChildShift) | (uint32_t)F;
             if (level[pos] > out->depth) out->depth = level[pos];
@@ -105,8 +122,10 @@ int pack_tree(const ccfd_forest_desc* d, int t, PackedTree* out) {
     // deepest level: contiguous tail of the breadth-first order, leaves only
     uint32_t lp = (uint32_t)order.size();
     while (lp > 0 && level[lp - 1] == out->depth) --lp;
+    if (big) lp = (uint32_t)order.size();  // keep every slot: "pos >= last_pos" never holds
     out->last_pos = lp;
-    memcpy(&out->last_vidx, &out->nodes[lp].thr, 4);
+    out->last_vidx = 0;
+    if (lp < order.size()) memcpy(&out->last_vidx, &out->nodes[lp].thr, 4);
     // top three levels in virtual complete order; a leaf repeats itself downwards
     auto is_leaf = [F](const PackedNode& n) { return (n.meta & kFeatMask) == (uint32_t)F; };
     TopNodes& tp = out->top;
@@ -154,8 +173,16 @@ int pack_forest(const ccfd_forest_desc* d, PackedForest* pf) {
     pf->trees.resize((size_t)d->n_trees);
     pf->top.resize((size_t)d->n_trees);
     PackedTree pt;
+    // A tree whose blob exceeds this can never fit a shared-memory stage on any sm_100 part: if the
+    // forest has one, lay the whole forest out for the GLOBAL kernel (second pass).
+    constexpr size_t kBigTreeBytes = 96 * 1024;
+    bool big = false;
+    for (int t = 0; t < d->n_trees && !big; ++t) {
+        const int64_t cnt = d->tree_offsets[t + 1] - d->tree_offsets[t];
+        big = (size_t)cnt * 16 > kBigTreeBytes;  // ~8 B per slot + 16 B per leaf (half the nodes) = 16 B per node
+    }
     for (int t = 0; t < d->n_trees; ++t) {
-        rc = pack_tree(d, t, &pt);
+        rc = pack_tree(d, t, big, &pt);
         if (rc != CCFD_OK) return rc;
         // the deepest level's leaf slots are never read (TreeRec::last_pos), so they are not stored
         const size_t node_bytes = (size_t)pt.last_pos * sizeof(PackedNode);

@@ -479,21 +479,47 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
 // Branch-free like the shared-memory descent: a row that has reached the deepest level (whose leaf
 // slots are not stored) is fed a synthetic self-looping leaf instead of a load.  Deep, ragged trees:
 // the warp stops as soon as all its lanes sit on leaves.
-template <bool NAN_AWARE>
-__device__ __forceinline__ uint32_t descend_global(const uint2* __restrict__ nodes, const float* __restrict__ xcol, int XS, int depth, uint32_t leaf_feat,
-                                                   uint32_t last_pos, uint32_t last_vidx) {
-    uint32_t pos = 0;
-    for (int d = 0; d < depth; ++d) {
-        uint2 nd = make_uint2(0u, (pos << kChildShift) | leaf_feat);
-        if (pos < last_pos) nd = __ldg(nodes + pos);
-        pos = step<NAN_AWARE>(nd, xcol[(nd.y & kFeatMask) * XS]);
-        if ((d & 3) == 3 && __all_sync(0xffffffffu, (nd.y & kFeatMask) == leaf_feat)) break;
+struct GlobalTree {
+    const uint2* nodes;
+    const uint8_t* vals;
+    int depth;
+    uint32_t last_pos, last_vidx;
+};
+
+// NT trees walked together by each thread: NT independent chains of dependent L2/HBM loads in flight.
+template <int NT, bool NAN_AWARE>
+__device__ __forceinline__ void descend_global(const GlobalTree (&gt)[NT], const float* __restrict__ xcol, int XS, uint32_t leaf_feat, uint32_t (&vidx)[NT]) {
+    uint32_t pos[NT];
+    int dmax = 0;
+#pragma unroll
+    for (int k = 0; k < NT; ++k) {
+        pos[k] = 0u;
+        dmax = max(dmax, gt[k].depth);
     }
-    uint32_t v = pos - last_pos + last_vidx;
-    if (pos < last_pos) v = __ldg(nodes + pos).x;
-    return v;
+    for (int d = 0; d < dmax; ++d) {
+        bool all_leaf = true;
+#pragma unroll
+        for (int k = 0; k < NT; ++k) {
+            uint2 nd = make_uint2(0u, (pos[k] << kChildShift) | leaf_feat);  // synthetic self-looping leaf
+            if (d < gt[k].depth && pos[k] < gt[k].last_pos) nd = __ldg(gt[k].nodes + pos[k]);
+            pos[k] = step<NAN_AWARE>(nd, xcol[(nd.y & kFeatMask) * XS]);
+            all_leaf = all_leaf && ((nd.y & kFeatMask) == leaf_feat);
+        }
+        if ((d & 3) == 3 && __all_sync(0xffffffffu, all_leaf)) break;
+    }
+#pragma unroll
+    for (int k = 0; k < NT; ++k) {
+        uint32_t v = pos[k] - gt[k].last_pos + gt[k].last_vidx;
+        if (pos[k] < gt[k].last_pos) v = __ldg(gt[k].nodes + pos[k]).x;
+        vidx[k] = v;
+    }
 }
 
+// kGlobalTrees trees per thread at a time.  Two help while the forest sits in L2 (latency bound: more
+// loads in flight); for forests around or beyond L2 capacity the walk is bound by L2/HBM sector
+// throughput and a second tree in flight only spreads the working set (measured: 858 -> 956 ms on
+// the 500-tree unbounded forest), so those run one.
+template <int kGlobalTrees>
 __global__ void __launch_bounds__(kTileThreads) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
     constexpr int S = kTileThreads, XS = S;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -506,16 +532,33 @@ __global__ void __launch_bounds__(kTileThreads) k_global(const ForestDev f, cons
     const bool any_nan = __syncthreads_or(my_nan) != 0;
 
     double acc0 = 0.0, acc1 = 0.0;
-    for (int t = 0; t < T; ++t) {
-        const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
-        const int4 raw2 = __ldg(reinterpret_cast<const int4*>(f.trees + t) + 1);
-        const uint8_t* tb = f.blob + (size_t)(uint32_t)raw.x * 16u;
-        const uint2* nodes = reinterpret_cast<const uint2*>(tb);
-        const uint32_t vidx = any_nan ? descend_global<true>(nodes, xs + tid, XS, raw.w, (uint32_t)F, raw2.x, raw2.y)
-                                      : descend_global<false>(nodes, xs + tid, XS, raw.w, (uint32_t)F, raw2.x, raw2.y);
-        const double2 v = __ldg(reinterpret_cast<const double2*>(tb + (uint32_t)raw.z) + vidx);
-        acc0 += v.x;
-        acc1 += v.y;
+    for (int t0 = 0; t0 < T; t0 += kGlobalTrees) {
+        GlobalTree gt[kGlobalTrees];
+#pragma unroll
+        for (int k = 0; k < kGlobalTrees; ++k) {
+            const int t = min(t0 + k, T - 1);
+            const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));
+            const int4 raw2 = __ldg(reinterpret_cast<const int4*>(f.trees + t) + 1);
+            const uint8_t* tb = f.blob + (size_t)(uint32_t)raw.x * 16u;
+            gt[k].nodes = reinterpret_cast<const uint2*>(tb);
+            gt[k].vals = tb + (uint32_t)raw.z;
+            gt[k].depth = (t0 + k < T) ? raw.w : 0;  // a slot past the last tree walks nothing and is ignored
+            gt[k].last_pos = (uint32_t)raw2.x;
+            gt[k].last_vidx = (uint32_t)raw2.y;
+        }
+        uint32_t vidx[kGlobalTrees];
+        if (any_nan)
+            descend_global<kGlobalTrees, true>(gt, xs + tid, XS, (uint32_t)F, vidx);
+        else
+            descend_global<kGlobalTrees, false>(gt, xs + tid, XS, (uint32_t)F, vidx);
+#pragma unroll
+        for (int k = 0; k < kGlobalTrees; ++k) {
+            if (t0 + k < T) {
+                const double2 v = __ldg(reinterpret_cast<const double2*>(gt[k].vals) + vidx[k]);
+                acc0 += v.x;  // tree order
+                acc1 += v.y;
+            }
+        }
     }
     if (tid < rows) {
         const double Td = (double)T;
@@ -682,7 +725,8 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_CUDA(cudaFuncSetAttribute(k_split_descend, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_global, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_global<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_global<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
 
     // STREAM ring geometry: a stage holds the largest tree and at least 128 rows of features.
     const uint32_t F = (uint32_t)f->dev.n_features;
@@ -755,6 +799,7 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         int spt = (a.n > (int64_t)f->sm_count * kConsumerThreads) ? 2 : 1;
         StreamPlan p = plan_stream(f, spt);
         if (!p.ok && spt == 2) p = plan_stream(f, spt = 1);
+        if (!f->info.stream_kernel_ok) p.ok = false;  // no group table was built for this forest
         if (!p.ok) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the STREAM kernel", f->dev.max_tree_bytes);
         const int64_t S = (int64_t)kConsumerThreads * spt;
         const int64_t n_batches = (a.n + S - 1) / S;
@@ -784,7 +829,7 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
 #undef CCFD_LAUNCH_STREAM
     } else if (kernel == CCFD_KERNEL_SPLIT) {
         uint32_t smem_bytes = 0;
-        if (!split_ok(f, &smem_bytes)) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the SPLIT kernel", f->dev.max_tree_bytes);
+        if (!split_ok(f, &smem_bytes) || !f->info.stream_kernel_ok) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the SPLIT kernel", f->dev.max_tree_bytes);
         if (!scratch) return ccfd_fail(CCFD_EINVAL, "SPLIT kernel needs scratch");
         const int64_t tiles = (a.n + kTileThreads - 1) / kTileThreads;
         if (tiles > 0x7FFFFFFFll) return ccfd_fail(CCFD_EINVAL, "too many rows for one launch");
@@ -802,7 +847,10 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
     } else if (kernel == CCFD_KERNEL_GLOBAL) {
         const int64_t tiles = (a.n + kTileThreads - 1) / kTileThreads;
         if (tiles > 0x7FFFFFFFll) return ccfd_fail(CCFD_EINVAL, "too many rows for one launch");
-        k_global<<<(unsigned)tiles, kTileThreads, tile_xs_bytes(f), stream>>>(f->dev, a, vec_ok);
+        if (f->info.model_bytes <= (int64_t)48 << 20)
+            k_global<2><<<(unsigned)tiles, kTileThreads, tile_xs_bytes(f), stream>>>(f->dev, a, vec_ok);
+        else
+            k_global<1><<<(unsigned)tiles, kTileThreads, tile_xs_bytes(f), stream>>>(f->dev, a, vec_ok);
     } else {
         return ccfd_fail(CCFD_EINVAL, "unknown kernel selector 0x%x", kernel);
     }

@@ -87,6 +87,25 @@ def test_from_sklearn_reads_a_fitted_forest():
     assert np.array_equal(bits(packed_emulator.predict_proba(blob, recs, 30, X[:500], top)), bits(rf.predict_proba(X[:500])))
 
 
+def test_big_tree_layout_dedups_leaf_values_and_keeps_every_slot():
+    from sklearn.ensemble import RandomForestClassifier
+
+    from ccfd_demo_summit_b200 import synth
+
+    X, y = synth.make_dataset(60000, seed=1, labels="hard")
+    rf = RandomForestClassifier(n_estimators=3, max_depth=None, random_state=0, n_jobs=-1).fit(X, y)
+    assert max(e.tree_.node_count for e in rf.estimators_) > 6144  # beyond any shared-memory stage
+    fa = converter.from_sklearn(rf)
+    blob, recs, top = packed_emulator.pack(fa)
+    for t, (off16, nbytes, values_off, depth, last_pos, last_vidx, *_r) in enumerate(recs):
+        n_src = rf.estimators_[t].tree_.node_count
+        assert last_pos == n_src and values_off == (n_src * 8 + 15) // 16 * 16
+        assert (nbytes - values_off) // 16 <= 4  # pure leaves: (1,0) and (0,1) only
+    rf.n_jobs = 1
+    got = packed_emulator.predict_proba(blob, recs, 30, X[:3000], top)
+    assert np.array_equal(bits(got), bits(rf.predict_proba(X[:3000])))
+
+
 @pytest.mark.parametrize("breakage", ["cycle", "feature", "one_child", "nan_thr", "offsets", "classes", "child_range"])
 def test_malformed_forests_are_rejected_with_valueerror(breakage):
     raw, *_ = load_golden("stumps")

@@ -112,6 +112,33 @@ def test_many_small_trees_take_the_table_free_stream_path(ccfd):
     forest.close()
 
 
+def test_unbounded_depth_forest_goes_through_the_global_kernel(ccfd):
+    """configs[2] in small: trees far beyond a shared-memory stage, pure leaves, p == 0.5 ties occur."""
+    from sklearn.ensemble import RandomForestClassifier
+
+    from ccfd_demo_summit_b200 import _lib, converter, synth
+
+    _, model = ccfd
+    X, y = synth.make_dataset(60000, seed=1, labels="hard")
+    rf = RandomForestClassifier(n_estimators=6, max_depth=None, random_state=0, n_jobs=-1).fit(X, y)
+    rf.n_jobs = 1
+    forest = model.Forest(converter.from_sklearn(rf))
+    assert forest.info["stream_kernel_ok"] == 0
+    Xq = synth.make_features(50000, seed=77)
+    P = rf.predict_proba(Xq)
+    got = _score_device(forest, Xq, "auto")
+    assert np.array_equal(bits(got), bits(P))
+    assert (P[:, 1] == 0.5).sum() > 0  # ties at the router's threshold exist: the operator matters
+    for ge in (False, True):
+        d = forest.decide(Xq, 0.5, ge=ge)
+        assert np.array_equal(d, (P[:, 1] >= 0.5) if ge else (P[:, 1] > 0.5))
+    got = forest.predict_proba(Xq[:300])  # host pointers, small: still GLOBAL
+    assert np.array_equal(bits(got), bits(P[:300]))
+    with pytest.raises(_lib.CcfdError):
+        _score_device(forest, Xq[:100], "stream")
+    forest.close()
+
+
 def test_fused_decision_matches_threshold_rule(ccfd):
     _, model = ccfd
     raw, X, P, _ = load_golden("deep")  # pure leaves: p is k/T, ties at the threshold really happen
