@@ -75,49 +75,60 @@ def time_sklearn(rf, X, budget_s=12.0, min_calls=3):
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons while the timed region runs."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled through NVML (what nvidia-smi reads) every few
+    milliseconds while the timed region runs; falls back to an nvidia-smi subprocess."""
+    REASONS = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
 
-    def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+    def __init__(self, index, period_s=0.004):
+        self.index, self.period_s = index, period_s
+        self.sm, self.mx, self.bits, self.stop, self.th, self.nvml = [], None, 0, threading.Event(), None, None
+
+    def _run(self):
+        n = self.nvml
+        while not self.stop.is_set():
+            try:
+                self.sm.append(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
+                self.bits |= int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period_s)
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "20"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            import pynvml
+
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.index]) if vis and vis.split(",")[self.index].isdigit() else self.index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.mx = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.nvml = pynvml
+            self.th = threading.Thread(target=self._run, daemon=True)
             self.th.start()
-        except OSError:
-            self.proc = None
+        except Exception:  # noqa: BLE001
+            self.nvml = None
         return self
 
     def __exit__(self, *a):
-        if self.proc:
-            time.sleep(0.15)
-            self.proc.terminate()
+        self.stop.set()
+        if self.th:
             self.th.join(timeout=2)
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            p = [x.strip() for x in ln.split(",")]
-            if len(p) < 7:
-                continue
-            try:
-                sm.append(float(p[0]))
-                mx.append(float(p[1]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, p[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        busy = sorted(sm)[len(sm) // 2:]  # upper half = under load
-        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        if not self.sm:
+            return self._smi_once()
+        reasons = sorted(k for k, bit in self.REASONS.items() if self.bits & bit)
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": float(self.mx), "reasons": reasons, "samples": len(self.sm),
+                "source": "nvml, sampled during the timed region"}
+
+    def _smi_once(self):
+        try:
+            out = subprocess.run(["nvidia-smi", f"--id={self.index}", "--query-gpu=clocks.sm,clocks.max.sm",
+                                  "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=10).stdout
+            sm, mx = (float(x) for x in out.strip().split(","))
+            return {"sm_mhz": sm, "sm_max_mhz": mx, "reasons": [], "samples": 1, "source": "nvidia-smi after the timed region"}
+        except Exception:  # noqa: BLE001
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": "unavailable"}
 
 
 def run_reference(args, rank, world):
