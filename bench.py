@@ -299,7 +299,7 @@ def main():
         sess = model.Session(forest, 1024, 4)
         rows = base[:1024 * 16].cpu().numpy()
         lat = []
-        for i in range(2300):
+        for i in range(10300):
             r = rows[(i % 16) * 1024:(i % 16 + 1) * 1024]
             t = time.perf_counter()
             sess.x[i % 4][:] = r           # producer writes the records into the pinned slot

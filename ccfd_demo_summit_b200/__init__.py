@@ -6,7 +6,7 @@ __all__ = ["ForestArrays", "from_sklearn", "from_arrays", "floor_to_float32", "C
 
 def __getattr__(name):
     # model.py needs the CUDA library; import it on first use so the converter works anywhere
-    if name in ("CcfdForestModel", "Forest", "Session", "validate_X"):
+    if name in ("CcfdForestModel", "Forest", "Session", "MultiGpuForest", "validate_X"):
         from . import model
 
         return getattr(model, name)

@@ -156,6 +156,51 @@ class Session:
     __del__ = close
 
 
+class MultiGpuForest:
+    """One forest replica per GPU inside one process; a bulk batch is cut into contiguous row ranges
+    (sharding.shard_bounds) and every GPU scores its range on its own streams.  Nothing is exchanged
+    between GPUs: rows are independent.  ctypes releases the GIL, so the per-GPU
+    calls overlap."""
+
+    def __init__(self, arrays: ForestArrays, devices=None):
+        n = _lib.check(_lib.lib().ccfd_device_count())
+        self.devices = list(range(n)) if devices is None else [int(d) for d in devices]
+        if not self.devices:
+            raise RuntimeError("no CUDA device")
+        self.forests = [Forest(arrays, d) for d in self.devices]
+        self.n_features, self.n_trees = arrays.n_features, arrays.n_trees
+
+    def predict_proba(self, X32: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        from .sharding import shard_bounds
+
+        n = X32.shape[0]
+        if out is None:
+            out = np.empty((n, 2), dtype=np.float64)
+        b = shard_bounds(n, len(self.forests))
+        errs = []
+
+        def work(g):
+            lo, hi = int(b[g]), int(b[g + 1])
+            try:
+                if hi > lo:
+                    self.forests[g].predict_proba(X32[lo:hi], out=out[lo:hi])
+            except Exception as e:  # noqa: BLE001
+                errs.append(e)
+
+        th = [threading.Thread(target=work, args=(g,)) for g in range(len(self.forests))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        if errs:
+            raise errs[0]
+        return out
+
+    def close(self):
+        for f in self.forests:
+            f.close()
+
+
 def load_model_file(path: str) -> ForestArrays:
     """``.npz`` written by ForestArrays.save, or a pickle/joblib of a fitted RandomForestClassifier."""
     if path.endswith(".npz"):
@@ -175,7 +220,8 @@ class CcfdForestModel:
 
     Configuration keeps the demo's environment-variable idiom (reference
     deploy/router.yaml:54-70): ``CCFD_MODEL_PATH`` (forest file), ``CCFD_DEVICE``
-    (GPU index), ``CCFD_SESSION_MAX_BATCH`` (requests up to this many rows take the
+    (GPU index), ``CCFD_DEVICES`` (comma-separated GPU indices: bulk requests are row-sharded over
+    them, one replica each), ``CCFD_SESSION_MAX_BATCH`` (requests up to this many rows take the
     CUDA-graph path; 0 disables it), ``FRAUD_THRESHOLD`` (same name and default as the
     router's).  A fitted forest or a ForestArrays can also be passed directly.
     """
@@ -191,6 +237,8 @@ class CcfdForestModel:
         arrays = model if isinstance(model, ForestArrays) else from_sklearn(model)
         device = int(os.environ.get("CCFD_DEVICE", "0")) if device is None else device
         self.forest = Forest(arrays, device)
+        devs = [int(d) for d in os.environ.get("CCFD_DEVICES", "").split(",") if d.strip() != ""]
+        self._multi = MultiGpuForest(arrays, devs) if len(devs) > 1 else None
         self.n_features_in_ = arrays.n_features
         self.classes_ = np.arange(arrays.n_classes)
         self.threshold = float(os.environ.get("FRAUD_THRESHOLD", "0.5"))
@@ -210,6 +258,8 @@ class CcfdForestModel:
                 slot = self._slot
                 self._slot = (slot + 1) % self._session.n_slots
                 P = self._session.score(slot, X32)
+        elif self._multi is not None and n >= 65536:
+            P = self._multi.predict_proba(X32)
         else:
             P = self.forest.predict_proba(X32)
         self._last = (X32[-1].copy(), P[-1].copy())
@@ -238,4 +288,7 @@ class CcfdForestModel:
         if self._session is not None:
             self._session.close()
             self._session = None
+        if self._multi is not None:
+            self._multi.close()
+            self._multi = None
         self.forest.close()

@@ -199,6 +199,18 @@ def test_session_slots_and_buckets(ccfd):
     forest.close()
 
 
+def test_session_large_bucket_captures_the_stream_kernel_in_a_graph(ccfd):
+    _, model = ccfd
+    raw, X, P, _ = load_golden("small_hard")
+    forest = model.Forest(_fa(raw))
+    s = model.Session(forest, max_batch=20000, n_slots=1)  # buckets 32 .. 16384, 20000: the last two run STREAM
+    big, want = np.tile(X, (14, 1))[:20000], np.tile(P, (14, 1))[:20000]
+    for n in (20000, 16385, 16384, 5000, 1):
+        assert np.array_equal(bits(s.score(0, big[:n])), bits(want[:n])), n
+    s.close()
+    forest.close()
+
+
 def test_nan_rows_follow_missing_go_to_left_in_large_batches(ccfd):
     _, model = ccfd
     from oracle import rf_oracle
@@ -266,6 +278,25 @@ def test_G2_easy_label_forest_bitwise_vs_sklearn(ccfd):
     Xn[::7, 3] = np.nan
     assert np.array_equal(bits(_score_device(forest, Xn, "stream")), bits(rf.predict_proba(Xn)))
     forest.close()
+
+
+def test_multi_gpu_row_sharding_in_one_process(full_forest):
+    """One replica per GPU, contiguous row ranges, no exchange: the concatenation of the shards is the
+    single-GPU result.  Uses every visible GPU (with one GPU it still exercises the sharded path)."""
+    from ccfd_demo_summit_b200 import converter, model
+
+    X, rf, forest = full_forest
+    multi = model.MultiGpuForest(converter.from_sklearn(rf))
+    assert len(multi.devices) == torch.cuda.device_count()
+    rows = X[:200_003]
+    want = forest.predict_proba(rows)
+    got = multi.predict_proba(rows)
+    assert np.array_equal(bits(got), bits(want))
+    if len(multi.devices) > 1:
+        two = model.MultiGpuForest(converter.from_sklearn(rf), devices=multi.devices[:2])
+        assert np.array_equal(bits(two.predict_proba(rows[:77])), bits(want[:77]))  # a shard may be empty
+        two.close()
+    multi.close()
 
 
 def test_large_batch_properties(full_forest):
