@@ -315,7 +315,12 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         best, calls = time_sklearn(rf, X)
+        rf.n_jobs = 1  # the bit-exact order; also the faster CPU path for tiny requests (no joblib dispatch)
+        t1 = time.perf_counter()
+        rf.predict_proba(X)
+        one_core = len(X) / (time.perf_counter() - t1)
         cpu = {"value": len(X) / best, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference", "cpu": cpu_model_name(),
+               "value_n_jobs_1": one_core,
                "sample": f"{len(X)} rows (configs[0] batch), best of {calls} calls, scikit-learn {__import__('sklearn').__version__} "
                          f"predict_proba n_jobs={os.cpu_count()} through the Seldon-shaped class"}
 

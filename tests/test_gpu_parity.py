@@ -203,9 +203,9 @@ def test_session_large_bucket_captures_the_stream_kernel_in_a_graph(ccfd):
     _, model = ccfd
     raw, X, P, _ = load_golden("small_hard")
     forest = model.Forest(_fa(raw))
-    s = model.Session(forest, max_batch=20000, n_slots=1)  # buckets 32 .. 16384, 20000: the last two run STREAM
-    big, want = np.tile(X, (14, 1))[:20000], np.tile(P, (14, 1))[:20000]
-    for n in (20000, 16385, 16384, 5000, 1):
+    s = model.Session(forest, max_batch=40000, n_slots=1)  # buckets 32 .. 32768 run SPLIT, the 40000 one STREAM
+    big, want = np.tile(X, (27, 1))[:40000], np.tile(P, (27, 1))[:40000]
+    for n in (40000, 32769, 32768, 16385, 5000, 1):
         assert np.array_equal(bits(s.score(0, big[:n])), bits(want[:n])), n
     s.close()
     forest.close()
