@@ -211,6 +211,80 @@ def test_session_large_bucket_captures_the_stream_kernel_in_a_graph(ccfd):
     forest.close()
 
 
+def test_concurrent_callers_on_their_own_streams(ccfd):
+    """A forest is immutable and the device-pointer entry point re-entrant: several threads score
+    different batches at once, each on its own stream (SPLIT takes its scratch per call)."""
+    import threading
+
+    _, model = ccfd
+    raw, X, P, _ = load_golden("small_hard")
+    forest = model.Forest(_fa(raw))
+    big, want = np.tile(X, (40, 1)), np.tile(P, (40, 1))  # 60,000 rows
+    results, errs = {}, []
+
+    def worker(k):
+        try:
+            st = torch.cuda.Stream()
+            n = [45000, 900, 33000, 64][k % 4] + k
+            assert k + n <= len(big)
+            xs = torch.from_numpy(big[k:k + n]).cuda()
+            out = torch.empty((n, 2), dtype=torch.float64, device="cuda")
+            torch.cuda.synchronize()
+            for _ in range(5):
+                forest.predict_proba_device(xs.data_ptr(), n, 30, out.data_ptr(), st.cuda_stream, "auto")
+            results[k] = (out.cpu().numpy(), n)
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in range(8)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs, errs
+    for k, (got, n) in results.items():
+        assert np.array_equal(bits(got), bits(want[k:k + n])), k
+    forest.close()
+
+
+def test_bad_arguments_come_back_as_error_codes_not_crashes(ccfd):
+    import ctypes
+
+    from ccfd_demo_summit_b200 import _lib
+
+    _, model = ccfd
+    raw, X, P, _ = load_golden("small_hard")
+    forest = model.Forest(_fa(raw))
+    L = _lib.lib()
+    xs = torch.from_numpy(X[:64]).cuda()
+    out = torch.empty((64, 2), dtype=torch.float64, device="cuda")
+    xp, op = ctypes.c_void_p(xs.data_ptr()), ctypes.c_void_p(out.data_ptr())
+    dev = _lib.DEVICE_PTRS
+    assert L.ccfd_predict_proba(forest.handle, xp, 0, 30, op, dev, None) == _lib.OK          # empty batch: nothing to do
+    assert L.ccfd_predict_proba(forest.handle, xp, -1, 30, op, dev, None) == _lib.EINVAL
+    assert L.ccfd_predict_proba(forest.handle, xp, 64, 29, op, dev, None) == _lib.EINVAL     # stride below n_features
+    assert L.ccfd_predict_proba(forest.handle, None, 64, 30, op, dev, None) == _lib.EINVAL
+    assert L.ccfd_predict_proba(forest.handle, xp, 64, 30, None, dev, None) == _lib.EINVAL
+    assert L.ccfd_predict_proba(None, xp, 64, 30, op, dev, None) == _lib.EINVAL
+    assert L.ccfd_predict_proba(forest.handle, xp, 64, 30, op, dev | 0x8000, None) == _lib.EINVAL  # unknown flag
+    assert L.ccfd_predict_proba(forest.handle, X[:64].ctypes.data_as(ctypes.c_void_p), 64, 30, op, _lib.ASYNC, None) == _lib.EINVAL
+    assert L.ccfd_predict_proba(forest.handle, xp, 64, 30, ctypes.c_void_p(out.data_ptr() + 8), dev, None) == _lib.EINVAL  # misaligned out
+    assert b"16-byte" in L.ccfd_last_error()
+    assert L.ccfd_predict_decision(forest.handle, xp, 64, 30, op, None, 0.5, 0, dev, None) == _lib.EINVAL
+    assert L.ccfd_predict_decision(forest.handle, xp, 64, 30, op, op, float("nan"), 0, dev, None) == _lib.EINVAL
+    h = ctypes.c_void_p()
+    assert L.ccfd_session_create(forest.handle, 0, 1, ctypes.byref(h)) == _lib.EINVAL
+    assert L.ccfd_session_create(forest.handle, 64, 0, ctypes.byref(h)) == _lib.EINVAL
+    d = _lib.ForestDesc()
+    assert L.ccfd_forest_create(ctypes.byref(d), 0, ctypes.byref(h)) == _lib.EINVAL
+    # still usable after all that
+    forest.predict_proba_device(xs.data_ptr(), 64, 30, out.data_ptr(), 0, "auto")
+    assert np.array_equal(bits(out.cpu().numpy()), bits(P[:64]))
+    forest.close()
+    with pytest.raises(ValueError):
+        model.Forest(_fa(raw), device=99)
+
+
 def test_nan_rows_follow_missing_go_to_left_in_large_batches(ccfd):
     _, model = ccfd
     from oracle import rf_oracle
