@@ -79,7 +79,7 @@ class Forest:
         return self._h
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and _lib is not None:  # _lib is None while the interpreter shuts down
             _lib.lib().ccfd_forest_destroy(self._h)
             self._h = ctypes.c_void_p()
 
@@ -148,7 +148,7 @@ class Session:
         return self.p[slot][:n].copy()
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and _lib is not None:
             self.x, self.p = [], []
             _lib.lib().ccfd_session_destroy(self._h)
             self._h = ctypes.c_void_p()
