@@ -9,13 +9,16 @@
 // multiple of 32) so that the data-dependent `x[feature]` fetch of 32 lanes always hits 32
 // different banks.
 //
-//   STREAM  throughput.  A persistent CTA keeps 512*SPT rows resident and streams the whole forest
-//           through a shared-memory ring with 1-D TMA bulk copies (cp.async.bulk + mbarrier
-//           complete_tx), one producer warp feeding 16 consumer warps.
+//   STREAM  throughput.  A persistent CTA per SM keeps 512*SPT rows resident; rows (as row-major
+//           chunks) and the forest (as tree groups) arrive through one shared-memory ring fed by
+//           1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx) from one producer warp;
+//           16 consumer warps transpose their own rows and walk TPT trees x SPT rows per thread.
+//           Per-tree metadata and the top three levels of every tree are kernel parameters
+//           (constant bank).
 //   SPLIT   latency.  Grid = row tiles x tree chunks so a 1-1024 row request still covers the
 //           chip; per-(tree,row) leaf values go to scratch and a second kernel adds them in tree
 //           order.
-//   GLOBAL  forests whose trees do not fit a shared-memory stage: nodes come from L2/HBM.
+//   GLOBAL  forests whose trees do not fit a shared-memory stage: nodes come from L1/L2/HBM.
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
