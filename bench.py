@@ -187,6 +187,8 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # rank 0's stdout carries exactly one JSON line: keep NCCL's own banner (NCCL_DEBUG=VERSION) off it
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
