@@ -187,9 +187,19 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
     torch.cuda.set_device(local_rank)
     if world > 1:
-        # rank 0's stdout carries exactly one JSON line: keep NCCL's own banner (NCCL_DEBUG=VERSION) off it
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # rank 0's stdout carries exactly one JSON line: NCCL prints its version banner to stdout when
+        # NCCL_DEBUG=VERSION (as on the benchmark boxes), so stdout points at stderr while it initialises
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     def barrier():
         if world > 1:
