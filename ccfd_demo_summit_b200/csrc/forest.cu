@@ -52,7 +52,7 @@ struct PackedTree {
     TopNodes top{};
 };
 
-// Breadth-first walk from the root; the two children of a node take adjacent positions.
+// Orders the nodes of one tree (the two children of a node always adjacent) and packs them.
 // `big` is the layout for trees that can never sit in shared memory (the GLOBAL kernel reads them
 // from L2/HBM): equal leaf values share one table entry (an unbounded-depth forest has pure leaves
 // only, so its 16-byte-per-leaf table collapses to two entries and the forest halves), and every
@@ -64,24 +64,88 @@ int pack_tree(const ccfd_forest_desc* d, int t, bool big, PackedTree* out) {
     if (cnt > kMaxNodesPerTree) return ccfd_fail(CCFD_EUNSUPPORTED, "tree %d has %lld nodes (max %lld)", t, (long long)cnt, (long long)kMaxNodesPerTree);
     const int F = d->n_features;
 
+    // ---- phase 1: the order of the nodes.  Whatever the order, the two children of a node are adjacent.
     std::vector<int32_t> order;          // position -> source node
     std::vector<uint32_t> level;         // position -> depth
     std::vector<uint8_t> seen((size_t)cnt, 0);
     order.reserve((size_t)cnt);
     level.reserve((size_t)cnt);
-    order.push_back(0);
-    level.push_back(0);
+    auto check_internal = [&](int32_t src) -> int {  // validates an internal node before its children are placed
+        const int64_t u = lo + src;
+        const int32_t l = d->left[u], r = d->right[u];
+        if (l < 0 && r < 0) return 0;  // leaf
+        if (l < 0 || r < 0) return ccfd_fail(CCFD_EINVAL, "tree %d node %d has exactly one child", t, src);
+        if (l >= cnt || r >= cnt || l == r) return ccfd_fail(CCFD_EINVAL, "tree %d node %d has a child out of range", t, src);
+        if (seen[l] || seen[r]) return ccfd_fail(CCFD_EINVAL, "tree %d is not a tree (node reached twice)", t);
+        seen[l] = seen[r] = 1;
+        return 1;
+    };
     seen[0] = 1;
+    if (!big) {
+        // breadth-first: every level contiguous, the deepest level (leaves only) last
+        order.push_back(0);
+        level.push_back(0);
+        for (size_t pos = 0; pos < order.size(); ++pos) {
+            const int rc = check_internal(order[pos]);
+            if (rc < 0) return rc;
+            if (rc == 1) {
+                const int64_t u = lo + order[pos];
+                order.push_back(d->left[u]);
+                order.push_back(d->right[u]);
+                level.push_back(level[pos] + 1);
+                level.push_back(level[pos] + 1);
+            }
+        }
+    } else {
+        // Blocks of three levels: a sibling pair, its (up to) two child pairs and four grandchild pairs,
+        // 14 nodes = 112 bytes, stored together.  A root-to-leaf path then crosses one 128-byte line
+        // (two at most) per three levels instead of one per level: fewer L2 sectors per path and three
+        // times as many levels per L1 line.  Blocks themselves are laid out breadth-first, top first.
+        struct BlockRoot {
+            int32_t a, b;  // the sibling pair that heads the block (b < 0: the tree root, which stands alone)
+            uint32_t depth;
+        };
+        std::vector<BlockRoot> blocks;
+        blocks.push_back(BlockRoot{0, -1, 0u});
+        std::vector<int32_t> cur, nxt;
+        for (size_t bi = 0; bi < blocks.size(); ++bi) {
+            const BlockRoot br = blocks[bi];
+            cur.clear();
+            cur.push_back(br.a);
+            if (br.b >= 0) cur.push_back(br.b);
+            for (int rel = 0; rel < 3; ++rel) {
+                nxt.clear();
+                for (int32_t src : cur) {
+                    order.push_back(src);
+                    level.push_back(br.depth + (uint32_t)rel);
+                    const int rc = check_internal(src);
+                    if (rc < 0) return rc;
+                    if (rc == 1) {
+                        nxt.push_back(d->left[lo + src]);
+                        nxt.push_back(d->right[lo + src]);
+                    }
+                }
+                if (rel == 2) {
+                    for (size_t i = 0; i + 1 < nxt.size(); i += 2) blocks.push_back(BlockRoot{nxt[i], nxt[i + 1], br.depth + 3u});
+                } else {
+                    cur.swap(nxt);
+                }
+            }
+        }
+    }
+    std::vector<uint32_t> pos_of((size_t)cnt, 0u);
+    for (size_t pos = 0; pos < order.size(); ++pos) pos_of[(size_t)order[pos]] = (uint32_t)pos;
+
+    // ---- phase 2: emit the packed nodes in that order
     out->nodes.clear();
     out->values.clear();
     out->depth = 0;
     std::map<std::pair<uint64_t, uint64_t>, uint32_t> seen_values;
     for (size_t pos = 0; pos < order.size(); ++pos) {
         const int64_t u = lo + order[pos];
-        const int32_t l = d->left[u], r = d->right[u];
+        const int32_t l = d->left[u];
         PackedNode pn;
-        if (l < 0 || r < 0) {
-            if (l >= 0 || r >= 0) return ccfd_fail(CCFD_EINVAL, "tree %d node %d has exactly one child", t, order[pos]);
+        if (l < 0) {
             uint32_t vidx = (uint32_t)(out->values.size() / 2);
             const double v0 = d->value[u * 2], v1 = d->value[u * 2 + 1];
             if (!std::isfinite(v0) || !std::isfinite(v1)) return ccfd_fail(CCFD_EINVAL, "tree %d node %d has a non-finite leaf value", t, order[pos]);
@@ -102,18 +166,12 @@ int pack_tree(const ccfd_forest_desc* d, int t, bool big, PackedTree* out) {
             pn.meta = ((uint32_t)pos << kChildShift) | (uint32_t)F;
             if (level[pos] > out->depth) out->depth = level[pos];
         } else {
-            if (l >= cnt || r >= cnt || l == r) return ccfd_fail(CCFD_EINVAL, "tree %d node %d has a child out of range", t, order[pos]);
-            if (seen[l] || seen[r]) return ccfd_fail(CCFD_EINVAL, "tree %d is not a tree (node reached twice)", t);
             const int32_t f = d->feature[u];
             if (f < 0 || f >= F) return ccfd_fail(CCFD_EINVAL, "tree %d node %d splits on feature %d (n_features %d)", t, order[pos], f, F);
             const float thr = d->threshold[u];
             if (std::isnan(thr)) return ccfd_fail(CCFD_EINVAL, "tree %d node %d has a NaN threshold", t, order[pos]);
-            seen[l] = seen[r] = 1;
-            const uint32_t child = (uint32_t)order.size();
-            order.push_back(l);
-            order.push_back(r);
-            level.push_back(level[pos] + 1);
-            level.push_back(level[pos] + 1);
+            const uint32_t child = pos_of[(size_t)l];
+            if (pos_of[(size_t)d->right[u]] != child + 1) return ccfd_fail(CCFD_EINVAL, "internal: siblings of tree %d node %d are not adjacent", t, order[pos]);
             pn.thr = thr;
             pn.meta = (child << kChildShift) | (d->missing_go_to_left[u] ? kMglBit : 0u) | (uint32_t)f;
         }
