@@ -32,7 +32,13 @@ constexpr int kConsumerWarps = 16;
 constexpr int kConsumerThreads = kConsumerWarps * 32;
 constexpr int kStreamThreads = kConsumerThreads + 32;  // + one producer warp
 constexpr int kMaxStages = 8;
-constexpr int kTileThreads = 256;                      // SPLIT and GLOBAL: one row per thread
+constexpr int kTileThreads = 256;                      // SPLIT: one row per thread
+// GLOBAL: one row per thread.  Bulk batches use one 768-row CTA per SM: all 24 warps of an SM then walk
+// the same two trees, so L1 holds those trees' upper levels (100 unbounded trees x 2 M rows: 256-thread
+// CTAs 8.97 ms, 512: 11.1, 768: 8.02, 1024: 8.11).  Batches too small to give every SM such a CTA use
+// 256-row CTAs.
+constexpr int kGlobalThreadsBulk = 768;
+constexpr int kGlobalThreadsSmall = 256;
 constexpr int kSplitStages = 2;
 
 __host__ __device__ constexpr uint32_t round_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
@@ -478,7 +484,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
 }
 
 // =============================================================================== GLOBAL kernel
-// One 256-row tile per CTA, several CTAs per SM to cover L2 latency; nodes via the read-only path.
+// One row tile per CTA; nodes via the read-only path (L1 -> L2 -> HBM).
 // Branch-free like the shared-memory descent: a row that has reached the deepest level (whose leaf
 // slots are not stored) is fed a synthetic self-looping leaf instead of a load.  Deep, ragged trees:
 // the warp stops as soon as all its lanes sit on leaves.
@@ -521,16 +527,16 @@ __device__ __forceinline__ void descend_global(const GlobalTree (&gt)[NT], const
 // kGlobalTrees trees per thread at a time: two independent chains of dependent loads per thread.
 // (Measured on unbounded-depth forests with the L1 carve-out below: 1 tree 12.1 ms, 2 trees 9.1 ms,
 // 4 trees 10.8 ms per 2 M rows x 100 trees.)
-template <int kGlobalTrees>
-__global__ void __launch_bounds__(kTileThreads) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
-    constexpr int S = kTileThreads, XS = S;
+template <int kGlobalTrees, int kGlobalThreads>
+__global__ void __launch_bounds__(kGlobalThreads) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
+    constexpr int S = kGlobalThreads, XS = S;
     extern __shared__ __align__(128) uint8_t smem[];
     float* xs = reinterpret_cast<float*>(smem);
     const int F = f.n_features, T = f.n_trees, tid = threadIdx.x;
     const int64_t row0 = (int64_t)blockIdx.x * S;
     const int rows = (int)((a.n - row0) < (int64_t)S ? (a.n - row0) : (int64_t)S);
-    for (int i = tid; i < XS; i += kTileThreads) xs[F * XS + i] = 0.0f;
-    const bool my_nan = load_tile<kTileThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+    for (int i = tid; i < XS; i += kGlobalThreads) xs[F * XS + i] = 0.0f;
+    const bool my_nan = load_tile<kGlobalThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
     const bool any_nan = __syncthreads_or(my_nan) != 0;
 
     double acc0 = 0.0, acc1 = 0.0;
@@ -727,16 +733,20 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_CUDA(cudaFuncSetAttribute(k_split_descend, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_global<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_global<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     {
         // GLOBAL walks nodes through L1/L2: leave most of the SM's 256 KB to L1 so that the upper levels
-        // of the trees the resident CTAs are on stay in L1 (3 CTAs of 32 KB instead of 7).  Measured on
-        // a 100-tree unbounded forest, 2 M rows: default carve-out 25.0 ms, 40 % 9.1 ms, 60 % 12.1 ms.
+        // of the trees the resident CTAs are on stay in L1.  Measured on a 100-tree unbounded forest,
+        // 2 M rows, 256-thread CTAs: default carve-out 25.0 ms, 40 % 9.1 ms, 60 % 12.1 ms.
         int carveout = 40;
         if (const char* e = getenv("CCFD_GLOBAL_CARVEOUT")) carveout = atoi(e);  // tuning knob
-        CCFD_CUDA(cudaFuncSetAttribute(k_global<1>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
-        CCFD_CUDA(cudaFuncSetAttribute(k_global<2>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
+#define CCFD_GLOBAL_ATTRS(NT_, TH_)                                                                                          \
+    CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin)); \
+    CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
+        CCFD_GLOBAL_ATTRS(1, kGlobalThreadsBulk)
+        CCFD_GLOBAL_ATTRS(2, kGlobalThreadsBulk)
+        CCFD_GLOBAL_ATTRS(1, kGlobalThreadsSmall)
+        CCFD_GLOBAL_ATTRS(2, kGlobalThreadsSmall)
+#undef CCFD_GLOBAL_ATTRS
     }
 
     // STREAM ring geometry: a stage holds the largest tree and at least 128 rows of features.
@@ -859,14 +869,21 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         k_split_descend<<<grid, kTileThreads, smem_bytes, stream>>>(f->dev, a, static_cast<double2*>(scratch), trees_per_cta, stage_bytes, vec_ok);
         k_split_reduce<<<(unsigned)((a.n + kReduceRows - 1) / kReduceRows), 128, 0, stream>>>(static_cast<const double2*>(scratch), f->dev.n_trees, a);
     } else if (kernel == CCFD_KERNEL_GLOBAL) {
-        const int64_t tiles = (a.n + kTileThreads - 1) / kTileThreads;
+        const bool bulk = a.n >= (int64_t)f->sm_count * kGlobalThreadsBulk;
+        const int threads = bulk ? kGlobalThreadsBulk : kGlobalThreadsSmall;
+        const int64_t tiles = (a.n + threads - 1) / threads;
         if (tiles > 0x7FFFFFFFll) return ccfd_fail(CCFD_EINVAL, "too many rows for one launch");
+        const uint32_t gsmem = round_up((uint32_t)(f->dev.n_features + 1) * (uint32_t)threads * 4u, 128u);
         int nt = 2;
         if (const char* e = getenv("CCFD_GLOBAL_NT")) nt = atoi(e);  // tuning knob
-        if (nt == 2)
-            k_global<2><<<(unsigned)tiles, kTileThreads, tile_xs_bytes(f), stream>>>(f->dev, a, vec_ok);
+        if (bulk && nt == 2)
+            k_global<2, kGlobalThreadsBulk><<<(unsigned)tiles, threads, gsmem, stream>>>(f->dev, a, vec_ok);
+        else if (bulk)
+            k_global<1, kGlobalThreadsBulk><<<(unsigned)tiles, threads, gsmem, stream>>>(f->dev, a, vec_ok);
+        else if (nt == 2)
+            k_global<2, kGlobalThreadsSmall><<<(unsigned)tiles, threads, gsmem, stream>>>(f->dev, a, vec_ok);
         else
-            k_global<1><<<(unsigned)tiles, kTileThreads, tile_xs_bytes(f), stream>>>(f->dev, a, vec_ok);
+            k_global<1, kGlobalThreadsSmall><<<(unsigned)tiles, threads, gsmem, stream>>>(f->dev, a, vec_ok);
     } else {
         return ccfd_fail(CCFD_EINVAL, "unknown kernel selector 0x%x", kernel);
     }
