@@ -75,6 +75,22 @@ class MicroBatcher:
         if self.fill == self.batch:
             self.flush()
 
+    def push_many(self, records) -> None:
+        """A consumer poll usually returns many messages: parse them in one native pass per slot fill
+        instead of one call per record (`records`: iterable of bytes, one transaction each)."""
+        records = list(records)
+        i = 0
+        while i < len(records):
+            take = min(len(records) - i, self.batch - self.fill)
+            blob = b"\n".join(records[i:i + take])
+            n = parse_rows_into(blob, self.s.x[self.slot][self.fill:self.fill + take], self.cols_in)
+            if n != take:
+                raise ValueError(f"{take} records held {n} rows")
+            self.fill += take
+            i += take
+            if self.fill == self.batch:
+                self.flush()
+
     def flush(self):
         """Submit the current slot (if it holds rows) and collect the previous one."""
         if self.fill == 0:

@@ -172,6 +172,14 @@ def test_kafka_shaped_replay_through_micro_batcher_matches_golden():
     mb.close()  # ragged tail of 232 rows
     assert mb.batches == 4 and len(lats) == 4
     assert np.array_equal(bits(got), bits(P[:1000]))
+    # the same stream delivered as consumer polls of 37 messages
+    got[:] = np.nan
+    mb = ingest.MicroBatcher(sess, batch=256, on_result=on_result)
+    recs = list(ingest.KafkaShapedProducer(X[:1000], fmt="json"))
+    for i in range(0, len(recs), 37):
+        mb.push_many(recs[i:i + 37])
+    mb.close()
+    assert mb.batches == 4 and np.array_equal(bits(got), bits(P[:1000]))
     sess.close()
     m.close()
 
