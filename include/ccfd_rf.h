@@ -85,14 +85,16 @@ CCFD_API int ccfd_device_count(void);
 /* Thread-local message of the last failure on this thread ("" if none). */
 CCFD_API const char* ccfd_last_error(void);
 
-/* Validate, re-lay-out (breadth-first, sibling-adjacent, 8-byte nodes) and upload.
+/* Validate, re-lay-out (8-byte nodes, the two children of a node adjacent; breadth-first for trees
+ * that fit shared memory, three-level blocks for larger ones) and upload.
  * Replaces: unpickling the forest inside the model image (reference
  * deploy/model/modelfull.json:24) — the library's equivalent of model load. */
 CCFD_API int ccfd_forest_create(const ccfd_forest_desc* desc, int device, ccfd_forest** out);
 CCFD_API int ccfd_forest_destroy(ccfd_forest* forest);
 /* The same validation and re-layout without a GPU: writes the packed image the kernels read
  * (all tree blobs back to back), 8 uint32 per tree {offset/16, bytes, leaf-value offset, depth,
- * first position of the deepest level, value index there, 0, 0} and, if top_nodes is not NULL,
+ * first position whose leaf slot is not stored (= node count when all are), value index there,
+ * 0, 0 (filled at create time)} and, if top_nodes is not NULL,
  * 14 uint32 per tree: the seven nodes of the top three levels as the STREAM kernel receives them.
  * Call with blob == NULL and tree_recs == NULL to learn *blob_bytes first.  Lets a deployment
  * build step (and the CPU tests) check a forest before it reaches a GPU; has no counterpart in
@@ -146,7 +148,9 @@ CCFD_API int ccfd_predict_proba_noalloc(ccfd_forest* forest, const float* X, int
                                         void* stream);
 
 /* Latency path: `n_slots` pinned host slots of `max_batch` rows, each with its
- * own device buffers and a pre-captured CUDA graph (copy in, score, copy out).
+ * own device buffers, scratch, a highest-priority stream and one pre-captured CUDA graph per
+ * power-of-two request size (copy in, score, result; requests of up to 4,096 rows have their last
+ * kernel write the result straight into the pinned buffer, larger ones copy out).
  * Replaces the per-request work of the Seldon wrapper around predict()
  * (requests arriving at reference deploy/router.yaml:65-68): the caller writes
  * rows straight into the slot and no allocation or Python happens per request. */
