@@ -39,6 +39,7 @@ constexpr int kTileThreads = 256;                      // SPLIT: one row per thr
 // 256-row CTAs.
 constexpr int kGlobalThreadsBulk = 768;
 constexpr int kGlobalThreadsSmall = 256;
+constexpr int kGlobalThreadsWide = 64;  // rows with so many features that 256 of them overflow shared memory
 constexpr int kSplitStages = 2;
 
 __host__ __device__ constexpr uint32_t round_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
@@ -746,6 +747,8 @@ int ccfd_kernels_init(ccfd_forest* f) {
         CCFD_GLOBAL_ATTRS(2, kGlobalThreadsBulk)
         CCFD_GLOBAL_ATTRS(1, kGlobalThreadsSmall)
         CCFD_GLOBAL_ATTRS(2, kGlobalThreadsSmall)
+        CCFD_GLOBAL_ATTRS(1, kGlobalThreadsWide)
+        CCFD_GLOBAL_ATTRS(2, kGlobalThreadsWide)
 #undef CCFD_GLOBAL_ATTRS
     }
 
@@ -869,21 +872,24 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         k_split_descend<<<grid, kTileThreads, smem_bytes, stream>>>(f->dev, a, static_cast<double2*>(scratch), trees_per_cta, stage_bytes, vec_ok);
         k_split_reduce<<<(unsigned)((a.n + kReduceRows - 1) / kReduceRows), 128, 0, stream>>>(static_cast<const double2*>(scratch), f->dev.n_trees, a);
     } else if (kernel == CCFD_KERNEL_GLOBAL) {
-        const bool bulk = a.n >= (int64_t)f->sm_count * kGlobalThreadsBulk;
-        const int threads = bulk ? kGlobalThreadsBulk : kGlobalThreadsSmall;
+        auto xs_bytes = [&](int threads) { return round_up((uint32_t)(f->dev.n_features + 1) * (uint32_t)threads * 4u, 128u); };
+        int threads = a.n >= (int64_t)f->sm_count * kGlobalThreadsBulk ? kGlobalThreadsBulk : kGlobalThreadsSmall;
+        if (threads == kGlobalThreadsBulk && xs_bytes(threads) > (uint32_t)f->smem_optin) threads = kGlobalThreadsSmall;
+        if (threads == kGlobalThreadsSmall && xs_bytes(threads) > (uint32_t)f->smem_optin) threads = kGlobalThreadsWide;
         const int64_t tiles = (a.n + threads - 1) / threads;
         if (tiles > 0x7FFFFFFFll) return ccfd_fail(CCFD_EINVAL, "too many rows for one launch");
-        const uint32_t gsmem = round_up((uint32_t)(f->dev.n_features + 1) * (uint32_t)threads * 4u, 128u);
+        const uint32_t gsmem = xs_bytes(threads);
         int nt = 2;
         if (const char* e = getenv("CCFD_GLOBAL_NT")) nt = atoi(e);  // tuning knob
-        if (bulk && nt == 2)
-            k_global<2, kGlobalThreadsBulk><<<(unsigned)tiles, threads, gsmem, stream>>>(f->dev, a, vec_ok);
-        else if (bulk)
-            k_global<1, kGlobalThreadsBulk><<<(unsigned)tiles, threads, gsmem, stream>>>(f->dev, a, vec_ok);
-        else if (nt == 2)
-            k_global<2, kGlobalThreadsSmall><<<(unsigned)tiles, threads, gsmem, stream>>>(f->dev, a, vec_ok);
-        else
-            k_global<1, kGlobalThreadsSmall><<<(unsigned)tiles, threads, gsmem, stream>>>(f->dev, a, vec_ok);
+#define CCFD_LAUNCH_GLOBAL(TH_)                                                                        \
+    do {                                                                                               \
+        if (nt == 2) k_global<2, TH_><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);     \
+        else k_global<1, TH_><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);             \
+    } while (0)
+        if (threads == kGlobalThreadsBulk) CCFD_LAUNCH_GLOBAL(kGlobalThreadsBulk);
+        else if (threads == kGlobalThreadsSmall) CCFD_LAUNCH_GLOBAL(kGlobalThreadsSmall);
+        else CCFD_LAUNCH_GLOBAL(kGlobalThreadsWide);
+#undef CCFD_LAUNCH_GLOBAL
     } else {
         return ccfd_fail(CCFD_EINVAL, "unknown kernel selector 0x%x", kernel);
     }

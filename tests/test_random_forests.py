@@ -34,7 +34,8 @@ def test_packed_walk_equals_oracle_on_random_forests(seed, n_trees, max_internal
 @pytest.mark.gpu
 @pytest.mark.parametrize("seed,n_trees,max_internal,F,skew,n", [
     (1, 7, 200, 30, 0.3, 5000), (2, 3, 1500, 30, 0.0, 40000), (3, 40, 60, 30, 0.9, 20000), (4, 1, 1, 1, 0.0, 700),
-    (5, 9, 300, 64, 0.5, 3000), (6, 12, 500, 7, 0.97, 17000), (7, 25, 40, 31, 0.2, 66000), (8, 2, 3000, 30, 0.1, 2049)])
+    (5, 9, 300, 64, 0.5, 3000), (6, 12, 500, 7, 0.97, 17000), (7, 25, 40, 31, 0.2, 66000), (8, 2, 3000, 30, 0.1, 2049),
+    (9, 5, 100, 200, 0.3, 900), (10, 3, 60, 255, 0.6, 120000)])  # rows too wide for the shared-memory kernels
 def test_cuda_kernels_equal_oracle_on_random_forests(seed, n_trees, max_internal, F, skew, n):
     import torch
 
