@@ -31,14 +31,20 @@ for c in range(n_cfg):
         X = np.nan_to_num(X, nan=0.5)  # NaN-free batches take the other code path
     want = rf_oracle.predict_proba_c(raw, X)
     forest = model.Forest(fa_of(raw))
-    xs = torch.from_numpy(X).cuda()
+    # row stride and base alignment vary too: dense+aligned takes the TMA path, the rest the generic loader
+    ld = F + int(rng.choice([0, 0, 1, 3, 8]))
+    off = int(rng.choice([0, 0, 1, 2]))
+    buf = torch.zeros(n * ld + 8, dtype=torch.float32, device="cuda")
+    xs = buf[off:off + n * ld].view(n, ld)
+    xs[:, :F] = torch.from_numpy(X).cuda()
+    cfg.update(ld=ld, off=off)
     st = torch.cuda.current_stream().cuda_stream
     kernels = ["global"] + (["stream", "split"] if forest.info["stream_kernel_ok"] else [])
     for k in kernels:
         m = min(n, 20000) if k == "split" else n
         out = torch.full((m, 2), -1.0, dtype=torch.float64, device="cuda")
         try:
-            forest.predict_proba_device(xs.data_ptr(), m, F, out.data_ptr(), st, k)
+            forest.predict_proba_device(xs.data_ptr(), m, ld, out.data_ptr(), st, k)
         except Exception as e:  # noqa: BLE001
             bad += 1
             print("ERROR", cfg, k, e, flush=True)
