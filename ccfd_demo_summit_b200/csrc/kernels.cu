@@ -655,6 +655,7 @@ __global__ void __launch_bounds__(128) k_split_reduce(const double2* __restrict_
     const int rows = (int)((a.n - row0) < (int64_t)kReduceRows ? (a.n - row0) : (int64_t)kReduceRows);
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     double acc0 = 0.0, acc1 = 0.0;
+    cudaGridDependencySynchronize();  // the descent kernel's scratch writes are complete and visible from here on
     for (int t0 = 0; t0 < T; t0 += kReduceTrees) {
         const int nt = min(kReduceTrees, T - t0);
         if (t0) __syncthreads();
@@ -870,7 +871,22 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         const uint32_t stage_bytes = round_up(f->dev.max_tree_bytes, 128u);
         dim3 grid((unsigned)tiles, (unsigned)chunks);
         k_split_descend<<<grid, kTileThreads, smem_bytes, stream>>>(f->dev, a, static_cast<double2*>(scratch), trees_per_cta, stage_bytes, vec_ok);
-        k_split_reduce<<<(unsigned)((a.n + kReduceRows - 1) / kReduceRows), 128, 0, stream>>>(static_cast<const double2*>(scratch), f->dev.n_trees, a);
+        {
+            // Programmatic dependent launch: the reduce grid may be scheduled while the descent drains and
+            // waits in cudaGridDependencySynchronize() for the descent's memory to be visible, which takes
+            // the second launch's latency off the request's critical path.
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3((unsigned)((a.n + kReduceRows - 1) / kReduceRows));
+            cfg.blockDim = dim3(128);
+            cfg.dynamicSmemBytes = 0;
+            cfg.stream = stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            CCFD_CUDA(cudaLaunchKernelEx(&cfg, k_split_reduce, static_cast<const double2*>(scratch), (int)f->dev.n_trees, a));
+        }
     } else if (kernel == CCFD_KERNEL_GLOBAL) {
         auto xs_bytes = [&](int threads) { return round_up((uint32_t)(f->dev.n_features + 1) * (uint32_t)threads * 4u, 128u); };
         int threads = a.n >= (int64_t)f->sm_count * kGlobalThreadsBulk ? kGlobalThreadsBulk : kGlobalThreadsSmall;
