@@ -269,3 +269,9 @@ extern "C" int ccfd_session_wait(ccfd_session* ss, int32_t slot) {
     CCFD_CUDA(cudaStreamSynchronize(s.stream));
     return CCFD_OK;
 }
+
+extern "C" int ccfd_session_run(ccfd_session* ss, int32_t slot, int64_t n_rows) {
+    int rc = ccfd_session_submit(ss, slot, n_rows);
+    if (rc != CCFD_OK) return rc;
+    return ccfd_session_wait(ss, slot);
+}

@@ -143,8 +143,7 @@ class Session:
         """Copy rows into the slot, run its graph, return a copy of the probabilities."""
         n = rows.shape[0]
         self.x[slot][:n] = rows
-        self.submit(slot, n)
-        self.wait(slot)
+        _lib.check(_lib.lib().ccfd_session_run(self._h, slot, n))
         return self.p[slot][:n].copy()
 
     def close(self):

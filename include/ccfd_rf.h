@@ -163,6 +163,9 @@ CCFD_API int ccfd_session_buffers(ccfd_session* session, int32_t slot, float** x
 CCFD_API int ccfd_session_submit(ccfd_session* session, int32_t slot, int64_t n_rows);
 /* Block until the slot's results are visible in its p buffer. */
 CCFD_API int ccfd_session_wait(ccfd_session* session, int32_t slot);
+/* submit + wait in one call, for callers that have nothing to overlap (one foreign-function call
+ * per request instead of two). */
+CCFD_API int ccfd_session_run(ccfd_session* session, int32_t slot, int64_t n_rows);
 
 /* Request text -> float32 rows, written straight into `dst` (typically a session slot's pinned x
  * buffer, so the bytes the GPU copies are produced in one pass).  Replaces the JSON decoding of the
