@@ -57,13 +57,23 @@ def parse_rows_into(body: bytes, dst: np.ndarray, cols_in: int | None = None) ->
     return int(n.value)
 
 
+def format_proba(P: np.ndarray) -> bytes:
+    """Native ``[[p0,p1],...]`` with shortest round-trip decimals (ccfd_format_proba)."""
+    P = np.ascontiguousarray(P, dtype=np.float64).reshape(-1, 2)
+    buf = ctypes.create_string_buffer(68 * P.shape[0] + 2)
+    n = ctypes.c_int64()
+    _lib.check(_lib.lib().ccfd_format_proba(P.ctypes.data_as(ctypes.c_void_p), P.shape[0], buf, len(buf), ctypes.byref(n)))
+    return buf.raw[: n.value]
+
+
 def encode_response(P: np.ndarray, metrics=None, tags=None) -> bytes:
-    msg = {"data": {"names": ["proba_0", "proba_1"], "ndarray": np.asarray(P).tolist()}, "meta": {}}
+    meta = {}
     if metrics:
-        msg["meta"]["metrics"] = metrics
+        meta["metrics"] = metrics
     if tags:
-        msg["meta"]["tags"] = tags
-    return json.dumps(msg).encode()
+        meta["tags"] = tags
+    return (b'{"data": {"names": ["proba_0", "proba_1"], "ndarray": ' + format_proba(P) + b'}, "meta": '
+            + json.dumps(meta).encode() + b"}")
 
 
 class SeldonApp:

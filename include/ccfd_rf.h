@@ -180,6 +180,12 @@ CCFD_API int ccfd_session_run(ccfd_session* session, int32_t slot, int64_t n_row
 CCFD_API int ccfd_parse_rows(const char* text, int64_t len, int32_t cols_in, int32_t cols_keep, float* dst,
                              int64_t cap_rows, int64_t* n_rows);
 
+/* The other direction: n_rows x 2 float64 probabilities -> "[[p0,p1],...]", the "ndarray" value of a
+ * Seldon response, using the shortest decimal strings that read back to exactly the same float64
+ * (what json.dumps produces, several times faster).  `cap` >= 68 * n_rows + 2 always suffices.
+ * Replaces the response encoding of the Seldon Python wrapper.  Pure host code. */
+CCFD_API int ccfd_format_proba(const double* p, int64_t n_rows, char* dst, int64_t cap, int64_t* len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -137,6 +137,10 @@ def test_unbounded_depth_forest_goes_through_the_global_kernel(ccfd):
     with pytest.raises(_lib.CcfdError):
         _score_device(forest, Xq[:100], "stream")
     forest.close()
+    m = model.CcfdForestModel(converter.from_sklearn(rf), session_max_batch=256)  # session graphs capture GLOBAL
+    assert np.array_equal(bits(m.predict(Xq[:100])), bits(P[:100]))
+    assert np.array_equal(bits(m.predict(Xq[:3000])), bits(P[:3000]))
+    m.close()
 
 
 def test_fused_decision_matches_threshold_rule(ccfd):

@@ -88,6 +88,18 @@ def test_encode_response_shape():
     assert msg["meta"]["metrics"][0]["key"] == "proba_1"
 
 
+def test_native_response_encoding_round_trips_every_float64():
+    rng = np.random.default_rng(3)
+    P = np.concatenate([rng.random((4000, 2)), np.array([[1.0, 0.0], [0.0, 1.0], [0.5, 0.5], [1e-300, 1 - 1e-16], [5e-324, 0.1],
+                                                         [1e-5, 123456789.125], [1e16, 1e22]])])
+    txt = sh.format_proba(P)
+    back = np.asarray(json.loads(txt), dtype=np.float64)
+    assert np.array_equal(back.view(np.uint64), P.view(np.uint64))
+    assert sh.format_proba(np.zeros((0, 2))) == b"[]"
+    with pytest.raises(ValueError):
+        sh.format_proba(np.array([[np.nan, 0.5]]))
+
+
 def test_coalescer_merges_concurrent_single_row_requests(rows):
     calls = []
 
