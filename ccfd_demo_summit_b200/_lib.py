@@ -69,10 +69,17 @@ def lib():
     global _lib
     if _lib is None:
         if not os.path.exists(LIB_PATH):
-            raise ImportError(
-                f"{LIB_PATH} is missing: build it with `python -m ccfd_demo_summit_b200.build` "
-                "(nvcc, sm_100a). There is no CPU fallback for the scoring path."
-            )
+            # a fresh checkout (the .so is not tracked): compile it in-tree if nvcc is here; there is no
+            # other way to score, so anything else is an error
+            try:
+                from . import build as _build
+
+                _build.build()
+            except Exception as e:  # noqa: BLE001
+                raise ImportError(
+                    f"{LIB_PATH} is missing and could not be built ({e}): run `python -m ccfd_demo_summit_b200.build` "
+                    "(nvcc, sm_100a). There is no CPU fallback for the scoring path."
+                ) from e
         handle = ctypes.CDLL(LIB_PATH)
         for name, restype, argtypes in SYMBOLS:
             fn = getattr(handle, name)  # AttributeError if the build lost a symbol
