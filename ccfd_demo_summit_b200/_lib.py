@@ -52,6 +52,7 @@ SYMBOLS = [
     ("ccfd_session_submit", c_int, [c_void_p, c_int32, c_int64]),
     ("ccfd_session_wait", c_int, [c_void_p, c_int32]),
     ("ccfd_session_run", c_int, [c_void_p, c_int32, c_int64]),
+    ("ccfd_cast_rows", c_int, [c_void_p, c_int32, c_int64, c_int64, c_int64, c_void_p, POINTER(c_int32)]),
     ("ccfd_format_proba", c_int, [c_void_p, c_int64, c_void_p, c_int64, POINTER(c_int64)]),
     ("ccfd_parse_rows", c_int, [c_char_p, c_int64, c_int32, c_int32, c_void_p, c_int64, POINTER(c_int64)]),
 ]

@@ -163,3 +163,57 @@ extern "C" int ccfd_format_proba(const double* p, int64_t n_rows, char* dst, int
     *len = q - dst;
     return CCFD_OK;
 }
+
+// float64 (or float32) request matrix -> dense float32 rows + the "contains infinity" verdict, in
+// one multi-threaded pass.  Replaces the cast and the finiteness scan of
+// ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625) for the common case of a
+// C-contiguous matrix as the Seldon wrapper hands it over (float64 after JSON decoding).  The
+// narrowing is the C cast (round to nearest even, overflow -> inf), bit-identical to numpy's astype.
+#include <thread>
+
+extern "C" int ccfd_cast_rows(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst,
+                              int32_t* has_inf) {
+    if (!src || !has_inf || n < 0 || n_cols < 1 || src_ld < n_cols) return ccfd_fail(CCFD_EINVAL, "bad argument");
+    if (!dst && src_is_f64) return ccfd_fail(CCFD_EINVAL, "dst may be null (scan only) for float32 input only");
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<int64_t>(std::max(1u, std::min(hw, 16u)), std::max<int64_t>(1, n * n_cols / 65536));
+    std::vector<int> inf_seen((size_t)nt, 0);
+    auto work = [&](int k) {
+        const int64_t r0 = n * k / nt, r1 = n * (k + 1) / nt;
+        int bad = 0;
+        for (int64_t r = r0; r < r1; ++r) {
+            if (!dst) {  // float32 rows that need no copy: finiteness scan only
+                const float* s = static_cast<const float*>(src) + r * src_ld;
+                for (int64_t c = 0; c < n_cols; ++c) bad |= (s[c] - s[c] != 0.0f) & (s[c] == s[c]);
+                continue;
+            }
+            float* d = dst + r * n_cols;
+            if (src_is_f64) {
+                const double* s = static_cast<const double*>(src) + r * src_ld;
+                for (int64_t c = 0; c < n_cols; ++c) {
+                    const float v = (float)s[c];
+                    d[c] = v;
+                    bad |= (v - v != 0.0f) & (v == v);  // inf - inf is NaN, NaN itself is allowed
+                }
+            } else {
+                const float* s = static_cast<const float*>(src) + r * src_ld;
+                for (int64_t c = 0; c < n_cols; ++c) {
+                    const float v = s[c];
+                    d[c] = v;
+                    bad |= (v - v != 0.0f) & (v == v);
+                }
+            }
+        }
+        inf_seen[(size_t)k] = bad;
+    };
+    if (nt == 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> th;
+        for (int k = 0; k < nt; ++k) th.emplace_back(work, k);
+        for (auto& t : th) t.join();
+    }
+    *has_inf = 0;
+    for (int b : inf_seen) *has_inf |= b;
+    return CCFD_OK;
+}

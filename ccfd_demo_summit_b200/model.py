@@ -25,13 +25,14 @@ def _ptr(a: np.ndarray):
     return a.ctypes.data_as(ctypes.c_void_p)
 
 
-def validate_X(X, n_features: int) -> np.ndarray:
+def validate_X(X, n_features: int, scratch=None) -> np.ndarray:
     """Mirror ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625).
 
     Any real dtype / memory order / nested list is accepted and cast to a C-ordered
     float32 matrix; NaN is allowed (trees route it by missing_go_to_left); 1-D
     input, zero rows, a wrong feature count and +-inf (or a float64 that overflows
-    float32) raise ValueError, as scikit-learn does.
+    float32) raise ValueError, as scikit-learn does.  ``scratch`` (optional, a dict the caller keeps)
+    lets repeated calls reuse one float32 buffer instead of faulting in fresh pages every request.
     """
     X = np.asarray(X)
     if X.dtype == object or X.dtype.kind not in "fiub":
@@ -46,9 +47,28 @@ def validate_X(X, n_features: int) -> np.ndarray:
         raise ValueError(f"Found array with 0 sample(s) (shape={X.shape}) while a minimum of 1 is required.")
     if X.shape[1] != n_features:
         raise ValueError(f"X has {X.shape[1]} features, but the forest is expecting {n_features} features as input.")
-    with np.errstate(over="ignore"):
-        X32 = np.ascontiguousarray(X, dtype=np.float32)
-    if np.isinf(X32).any():
+    if X.dtype in (np.float64, np.float32) and X.strides[1] == X.itemsize and X.strides[0] % X.itemsize == 0 \
+            and X.strides[0] >= X.shape[1] * X.itemsize and X.size >= 4096:
+        # the usual case (a C-ordered float matrix): cast and finiteness scan in one native, threaded pass
+        dense32 = X.dtype == np.float32 and X.flags.c_contiguous
+        if dense32:
+            X32 = X  # dense float32 rows are used in place
+        elif scratch is not None:
+            buf = scratch.get("buf")
+            if buf is None or buf.size < X.size:
+                buf = scratch["buf"] = np.empty(X.size, dtype=np.float32)
+            X32 = buf[: X.size].reshape(X.shape)
+        else:
+            X32 = np.empty(X.shape, dtype=np.float32)
+        bad = ctypes.c_int32()
+        _lib.check(_lib.lib().ccfd_cast_rows(_ptr(X), int(X.dtype == np.float64), X.shape[0], X.shape[1],
+                                             X.strides[0] // X.itemsize, None if dense32 else _ptr(X32), ctypes.byref(bad)))
+        has_inf = bool(bad.value)
+    else:
+        with np.errstate(over="ignore"):
+            X32 = np.ascontiguousarray(X, dtype=np.float32)
+        has_inf = bool(np.isinf(X32).any())
+    if has_inf:
         raise ValueError("Input X contains infinity or a value too large for dtype('float32').")
     return X32
 
@@ -244,13 +264,17 @@ class CcfdForestModel:
         smb = int(os.environ.get("CCFD_SESSION_MAX_BATCH", "1024")) if session_max_batch is None else session_max_batch
         self._session = Session(self.forest, smb, n_slots=2) if smb > 0 else None
         self._lock = threading.Lock()
+        self._tls = threading.local()  # per-thread cast buffer (Seldon may run threaded workers)
         self._slot = 0
         self._last = None
 
     def predict(self, X, feature_names=None, meta=None):
         """The Seldon wrapper passes the names positionally; like scikit-learn on a forest fitted
         from an ndarray, they are not used to reorder columns."""
-        X32 = validate_X(X, self.n_features_in_)
+        tl = self._tls
+        if not hasattr(tl, "scratch"):
+            tl.scratch = {}
+        X32 = validate_X(X, self.n_features_in_, tl.scratch)
         n = X32.shape[0]
         if self._session is not None and n <= self._session.max_batch:
             with self._lock:

@@ -180,6 +180,15 @@ CCFD_API int ccfd_session_run(ccfd_session* session, int32_t slot, int64_t n_row
 CCFD_API int ccfd_parse_rows(const char* text, int64_t len, int32_t cols_in, int32_t cols_keep, float* dst,
                              int64_t cap_rows, int64_t* n_rows);
 
+/* A float64 (src_is_f64 != 0) or float32 matrix of n rows x n_cols, row stride src_ld elements, ->
+ * dense float32 rows in dst, and *has_inf = 1 if any narrowed value is +-inf (NaN is allowed), in one
+ * multi-threaded pass.  Replaces the cast and the finiteness scan of
+ * ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625); the narrowing is
+ * bit-identical to numpy's astype(float32).  dst == NULL with float32 input scans only (rows that are
+ * already dense float32 need no copy).  Pure host code. */
+CCFD_API int ccfd_cast_rows(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst,
+                            int32_t* has_inf);
+
 /* The other direction: n_rows x 2 float64 probabilities -> "[[p0,p1],...]", the "ndarray" value of a
  * Seldon response, using the shortest decimal strings that read back to exactly the same float64
  * (what json.dumps produces, several times faster).  `cap` >= 68 * n_rows + 2 always suffices.
