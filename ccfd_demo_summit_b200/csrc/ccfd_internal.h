@@ -11,15 +11,23 @@
 #include "ccfd_rf.h"
 
 // ----------------------------------------------------------------------------------------------
-// Packed node, 8 bytes.  Trees are laid out breadth-first with the two children of a node in
-// adjacent slots, so one child position serves both: next = child + (go_right ? 1 : 0).
+// Packed node, 8 bytes.  Trees are laid out with the two children of a node in adjacent slots, so
+// one child reference serves both: next = child + (go_right ? one slot : 0).
 //   internal : thr  = largest fp32 <= sklearn's fp64 threshold      (x <= thr  <=>  go left)
-//              meta = child_pos << 9 | missing_go_to_left << 8 | feature
-//   leaf     : thr  = bit pattern of the tree-local leaf-value index (a non-negative tiny float)
-//              meta = own_pos << 9 | n_features   -> reads the all-zero dummy feature row, 0 <= thr
-//                     always holds, so a leaf steps to itself and fixed-trip loops need no leaf test.
-// Breadth-first order keeps each level contiguous: the top levels (<= 16 nodes = 128 B) are
-// shared-memory bank-conflict free however the 32 rows of a warp spread over them.
+//   leaf     : thr  = bit pattern of the tree-local leaf-value index (a non-negative tiny float);
+//              its feature is n_features -> it reads the all-zero dummy feature row, 0 <= thr always
+//              holds and its child reference is itself, so a leaf steps to itself and fixed-trip
+//              loops need no leaf test.
+// Two encodings of `meta`, one per forest (TreeRec::group_flags bit 2, ForestDev::wide_nodes):
+//   compact (every tree <= 96 KB: the shared-memory kernels' format)
+//              meta = child_byte_offset << 16 | feature << 8 | missing_go_to_left
+//              The child reference is a BYTE offset from the tree's first node, so the next node's
+//              shared-memory address is base + (meta >> 16) (+ 8 for the right child): one shift-add
+//              instead of shift, add, scale, add per level of every row.
+//   wide    (forests with a larger tree: GLOBAL kernel only)
+//              meta = child_slot << 9 | missing_go_to_left << 8 | feature
+// Breadth-first order (compact) keeps each level contiguous: the top levels (<= 16 nodes = 128 B)
+// are shared-memory bank-conflict free however the 32 rows of a warp spread over them.
 // ----------------------------------------------------------------------------------------------
 struct PackedNode {
     float thr;
@@ -27,10 +35,32 @@ struct PackedNode {
 };
 static_assert(sizeof(PackedNode) == 8, "node must be 8 bytes");
 
-constexpr uint32_t kFeatMask = 0xFFu;
-constexpr uint32_t kMglBit = 0x100u;
-constexpr int kChildShift = 9;
 constexpr int64_t kMaxNodesPerTree = (int64_t)1 << 23;
+constexpr uint32_t kWideNodesFlag = 4u;  // TreeRec::group_flags
+
+// Field access for the two encodings.  child() is in node slots.
+template <bool WIDE>
+struct NodeFmt;
+template <>
+struct NodeFmt<true> {
+    static __host__ __device__ __forceinline__ uint32_t feature(uint32_t meta) { return meta & 0xFFu; }
+    static __host__ __device__ __forceinline__ bool mgl(uint32_t meta) { return (meta & 0x100u) != 0u; }
+    static __host__ __device__ __forceinline__ uint32_t child(uint32_t meta) { return meta >> 9; }
+    static __host__ __device__ __forceinline__ uint32_t make(uint32_t child_slot, bool mgl, uint32_t feature) {
+        return (child_slot << 9) | (mgl ? 0x100u : 0u) | feature;
+    }
+};
+template <>
+struct NodeFmt<false> {
+    static __host__ __device__ __forceinline__ uint32_t feature(uint32_t meta) { return (meta >> 8) & 0xFFu; }
+    static __host__ __device__ __forceinline__ bool mgl(uint32_t meta) { return (meta & 1u) != 0u; }
+    static __host__ __device__ __forceinline__ uint32_t child(uint32_t meta) { return meta >> 19; }
+    static __host__ __device__ __forceinline__ uint32_t child_bytes(uint32_t meta) { return meta >> 16; }
+    static __host__ __device__ __forceinline__ uint32_t make(uint32_t child_slot, bool mgl, uint32_t feature) {
+        return (child_slot << 19) | (feature << 8) | (mgl ? 1u : 0u);
+    }
+};
+constexpr int64_t kMaxCompactSlots = 8192;  // 16-bit byte offsets
 
 // Per-tree record read by the kernels (32 bytes, two 16-byte uniform loads).
 struct TreeRec {
@@ -45,7 +75,8 @@ struct TreeRec {
     uint32_t last_vidx;
     // filled when the forest is bound to a device (STREAM ring geometry), 0 in ccfd_forest_pack output
     uint32_t rel_off;      // byte offset of the blob inside its tree group (= inside a ring stage)
-    uint32_t group_flags;  // bit 0: first tree of its group, bit 1: last tree of its group
+    uint32_t group_flags;  // bit 0: first tree of its group, bit 1: last tree of its group (both set at bind
+                           // time), bit 2: wide node encoding (set by the packer)
 };
 static_assert(sizeof(TreeRec) == 32, "TreeRec must be 32 bytes");
 
@@ -92,6 +123,7 @@ struct ForestDev {
     uint32_t max_depth;
     uint32_t stage_bytes;    // STREAM ring stage: >= largest blob and >= 128 rows of features
     uint32_t chunk_rows;     // rows of a row chunk that fit a stage, multiple of 32
+    uint32_t wide_nodes;     // node encoding: 0 compact, 1 wide (see PackedNode)
 };
 
 struct ccfd_forest {

@@ -133,6 +133,7 @@ int pack_tree(const ccfd_forest_desc* d, int t, bool big, PackedTree* out) {
             }
         }
     }
+    if (!big && (int64_t)order.size() > kMaxCompactSlots) return ccfd_fail(CCFD_EUNSUPPORTED, "internal: tree %d too large for the compact encoding", t);
     std::vector<uint32_t> pos_of((size_t)cnt, 0u);
     for (size_t pos = 0; pos < order.size(); ++pos) pos_of[(size_t)order[pos]] = (uint32_t)pos;
 
@@ -163,7 +164,7 @@ int pack_tree(const ccfd_forest_desc* d, int t, bool big, PackedTree* out) {
                 out->values.push_back(v1);
             }
             memcpy(&pn.thr, &vidx, 4);
-            pn.meta = ((uint32_t)pos << kChildShift) | (uint32_t)F;
+            pn.meta = big ? NodeFmt<true>::make((uint32_t)pos, false, (uint32_t)F) : NodeFmt<false>::make((uint32_t)pos, false, (uint32_t)F);
             if (level[pos] > out->depth) out->depth = level[pos];
         } else {
             const int32_t f = d->feature[u];
@@ -173,7 +174,8 @@ int pack_tree(const ccfd_forest_desc* d, int t, bool big, PackedTree* out) {
             const uint32_t child = pos_of[(size_t)l];
             if (pos_of[(size_t)d->right[u]] != child + 1) return ccfd_fail(CCFD_EINVAL, "internal: siblings of tree %d node %d are not adjacent", t, order[pos]);
             pn.thr = thr;
-            pn.meta = (child << kChildShift) | (d->missing_go_to_left[u] ? kMglBit : 0u) | (uint32_t)f;
+            const bool mgl = d->missing_go_to_left[u] != 0;
+            pn.meta = big ? NodeFmt<true>::make(child, mgl, (uint32_t)f) : NodeFmt<false>::make(child, mgl, (uint32_t)f);
         }
         out->nodes.push_back(pn);
     }
@@ -185,12 +187,13 @@ int pack_tree(const ccfd_forest_desc* d, int t, bool big, PackedTree* out) {
     out->last_vidx = 0;
     if (lp < order.size()) memcpy(&out->last_vidx, &out->nodes[lp].thr, 4);
     // top three levels in virtual complete order; a leaf repeats itself downwards
-    auto is_leaf = [F](const PackedNode& n) { return (n.meta & kFeatMask) == (uint32_t)F; };
+    auto feature_of = [big](const PackedNode& n) { return big ? NodeFmt<true>::feature(n.meta) : NodeFmt<false>::feature(n.meta); };
+    auto is_leaf = [&](const PackedNode& n) { return feature_of(n) == (uint32_t)F; };
     TopNodes& tp = out->top;
     tp.n[0] = out->nodes[0];
     for (int parent = 0; parent < 3; ++parent) {
         const PackedNode& pn = tp.n[parent];
-        const uint32_t c = pn.meta >> kChildShift;
+        const uint32_t c = big ? NodeFmt<true>::child(pn.meta) : NodeFmt<false>::child(pn.meta);
         tp.n[2 * parent + 1] = out->nodes[c];
         tp.n[2 * parent + 2] = is_leaf(pn) ? out->nodes[c] : out->nodes[c + 1];
     }
@@ -258,7 +261,8 @@ int pack_forest(const ccfd_forest_desc* d, PackedForest* pf) {
         tr.depth = pt.depth;
         tr.last_pos = pt.last_pos;
         tr.last_vidx = pt.last_vidx;
-        tr.rel_off = tr.group_flags = 0;
+        tr.rel_off = 0;
+        tr.group_flags = big ? kWideNodesFlag : 0u;
         pf->top[(size_t)t] = pt.top;
         pf->n_nodes += (int64_t)pt.nodes.size();
         pf->n_leaves += (int64_t)pt.values.size() / 2;

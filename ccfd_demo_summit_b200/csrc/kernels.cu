@@ -94,6 +94,24 @@ __device__ __forceinline__ bool named_bar_or(int id, int nthreads, bool pred) {
         : "memory");
     return r != 0;
 }
+// Shared-memory loads by 32-bit shared-window address.  The descent keeps node addresses in this form
+// so that "next node" is one select and one shift-add (see descend).  volatile: ordered after the
+// mbarrier wait that published the bytes.
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ double2 lds128d(uint32_t addr) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
 // streaming 128-bit load: rows are read once, keep them out of L1
 __device__ __forceinline__ float4 ld_stream4(const float4* p) {
     float4 v;
@@ -109,9 +127,9 @@ __device__ __forceinline__ float4 ld_stream4(const float4* p) {
 // row, a different f per lane) never conflict.  The price is bank conflicts on these transposed
 // stores, paid once per row instead of once per node visit; the STREAM kernel's main path avoids
 // even that (see transpose_group).
-template <int NT, int S>
+template <int NT, int S, bool XB = false>
 __device__ __forceinline__ bool load_tile(float* xs, const float* __restrict__ src, int rows, int64_t ld, int F, bool vec_ok, int tid) {
-    constexpr int XS = S;
+    auto at = [](int c, int r) { return XB ? ((r >> 6) * 2048 + c * 64 + (r & 63)) : (c * S + r); };  // see XStrided / XBlocked
     bool nan = false;
     const int total = rows * F;
     if (vec_ok) {
@@ -125,7 +143,7 @@ __device__ __forceinline__ bool load_tile(float* xs, const float* __restrict__ s
             const float qq[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                xs[c * XS + r] = qq[j];
+                xs[at(c, r)] = qq[j];
                 nan |= (qq[j] != qq[j]);
                 if (++c == F) {
                     c = 0;
@@ -136,14 +154,14 @@ __device__ __forceinline__ bool load_tile(float* xs, const float* __restrict__ s
         for (int e = (nvec << 2) + tid; e < total; e += NT) {
             const int r = e / F, c = e - r * F;
             const float v = __ldg(src + e);
-            xs[c * XS + r] = v;
+            xs[at(c, r)] = v;
             nan |= (v != v);
         }
     } else {
         for (int e = tid; e < total; e += NT) {
             const int r = e / F, c = e - r * F;
             const float v = __ldg(src + (int64_t)r * ld + c);
-            xs[c * XS + r] = v;
+            xs[at(c, r)] = v;
             nan |= (v != v);
         }
     }
@@ -151,7 +169,7 @@ __device__ __forceinline__ bool load_tile(float* xs, const float* __restrict__ s
         const int pad = (S - rows) * F;
         for (int e = tid; e < pad; e += NT) {
             const int r = e / F, c = e - r * F;
-            xs[c * XS + rows + r] = 0.0f;
+            xs[at(c, rows + r)] = 0.0f;
         }
     }
     return nan;
@@ -161,46 +179,89 @@ __device__ __forceinline__ bool load_tile(float* xs, const float* __restrict__ s
 // One step per level, no branch: x <= thr picks the left slot of the sibling pair, anything else
 // (including NaN on the NaN-free path) the right one.  With NAN_AWARE a NaN follows the node's
 // missing_go_to_left bit (SK/tree/_tree.pyx:984-988).  Leaves step to themselves.
-template <bool NAN_AWARE>
-__device__ __forceinline__ uint32_t step(const uint2 nd, const float x) {
-    bool left = x <= __uint_as_float(nd.x);
-    if (NAN_AWARE) left = (x != x) ? ((nd.y & kMglBit) != 0u) : left;
-    return (nd.y >> kChildShift) + (left ? 0u : 1u);
+template <bool NAN_AWARE, bool WIDE>
+__device__ __forceinline__ bool goes_right(const uint2 nd, const float x) {
+    bool right = !(x <= __uint_as_float(nd.x));
+    if (NAN_AWARE) right = (x != x) ? !NodeFmt<WIDE>::mgl(nd.y) : right;
+    return right;
 }
 
-// What a thread needs to walk one tree whose blob sits in shared memory.
+// What a thread needs to walk one tree whose blob sits in shared memory (compact node encoding:
+// child references are byte offsets from the first node).  Addresses are 32-bit shared-window
+// addresses.
 struct TreeView {
-    const uint2* nodes;    // node slots [0, last_pos): the deepest level's leaf slots are not stored
-    const double2* vals;   // (v0, v1) per leaf
+    uint32_t nodes;        // node slots [nodes, nodes + last_off): the deepest level's leaf slots are not stored
+    uint32_t vals;         // (v0, v1) per leaf, 16 bytes each
     const uint2* top;      // seven top nodes in the constant bank (TOP kernels) or null
     int depth;
-    uint32_t last_pos, last_vidx;
+    uint32_t last_off;     // byte offset of the first slot of the deepest level
+    uint32_t last_voff;    // byte offset, from vals, of that slot's leaf value
 };
+
+// Where a thread finds x[feature] of its rows.  Two layouts of the transposed rows:
+//   strided  xs[feature * XS + row] (XS a multiple of 32): any feature count.
+//   blocked  64-row blocks of 32 feature rows (8 KB, block-aligned in the shared window):
+//            address = block | feature << 8 | row_in_block << 2.  The node's meta word carries the
+//            feature at bits 8..15 already, so the x address is ONE and-or of meta with the thread's
+//            own address bits.  Needs n_features + 1 <= 32.
+// Both give bank = row % 32 whatever the feature: the data-dependent reads never conflict.
+constexpr int kBlockRows = 64;
+constexpr int kBlockFloats = 32 * kBlockRows;      // 2048 floats = 8 KB
+constexpr uint32_t kBlockBytes = kBlockFloats * 4u;
+constexpr int kMaxBlockedFeatures = 31;            // + the all-zero dummy row = 32
+
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+
+template <int STRIDE>
+struct XStrided {
+    const float* xcol;  // &xs[row of this thread]
+    int XS;
+    __device__ __forceinline__ float get(uint32_t meta, int i) const { return xcol[NodeFmt<false>::feature(meta) * XS + i * STRIDE]; }
+};
+// STRIDE_ROWS: distance in rows between a thread's consecutive rows (a multiple of kBlockRows)
+template <int STRIDE_ROWS>
+struct XBlocked {
+    uint32_t tb;  // shared address of x[feature 0] of this thread's first row; bits 8..12 are zero
+    __device__ __forceinline__ float get(uint32_t meta, int i) const {
+        return lds_f32(((meta & 0x1F00u) | tb) + (uint32_t)i * (uint32_t)(STRIDE_ROWS / kBlockRows) * kBlockBytes);
+    }
+};
+// float index of (feature 0, row s) in the blocked layout
+__device__ __forceinline__ int blocked_row(int s) { return (s >> 6) * kBlockFloats + (s & (kBlockRows - 1)); }
 
 // NT trees x SPT rows = NT*SPT independent pointer chases per thread, interleaved so that the
 // shared-memory latency of one is covered by the others.  With TOP the first three levels come
 // from the kernel parameters (constant bank, warp-uniform loads: no shared-memory bandwidth) and
 // the level-1 / level-2 nodes are picked with selects.  Every tree runs exactly `depth` steps, so
 // a row ends on its leaf; rows that end on the deepest level (nearly all rows of a depth-limited
-// forest) get their value index from the position, the few others read their leaf slot.
-template <int SPT, int NT, int STRIDE, bool NAN_AWARE, bool TOP>
-__device__ __forceinline__ void descend(const TreeView (&tv)[NT], const float* __restrict__ xcol, int XS, uint32_t (&vidx)[NT][SPT]) {
-    uint32_t pos[NT][SPT];
+// forest) get their value's place from the slot's place, the few others read their leaf slot.
+// Per level and chain: node load, feature -> x address, x load, compare, select the base (left or
+// right sibling), shift-add the child offset.
+// Result: vaddr = shared address of the row's leaf value.
+template <int SPT, int NT, bool NAN_AWARE, bool TOP, class XA>
+__device__ __forceinline__ void descend(const TreeView (&tv)[NT], const XA xa, uint32_t (&vaddr)[NT][SPT]) {
+    using Fmt = NodeFmt<false>;
+    uint32_t at[NT][SPT];  // shared address of the current slot
     int d0 = 0;
     if (TOP) {
 #pragma unroll
         for (int k = 0; k < NT; ++k) {
             const uint2* top = tv[k].top;
             const uint2 t0 = top[0], t1 = top[1], t2 = top[2], t3 = top[3], t4 = top[4], t5 = top[5], t6 = top[6];
+            const uint32_t nb = tv[k].nodes, nb8 = nb + 8u;
 #pragma unroll
             for (int i = 0; i < SPT; ++i) {
-                const float* xc = xcol + i * STRIDE;
-                const bool r0 = step<NAN_AWARE>(t0, xc[(t0.y & kFeatMask) * XS]) != (t0.y >> kChildShift);
+                const bool r0 = goes_right<NAN_AWARE, false>(t0, xa.get(t0.y, i));
                 const uint2 a = r0 ? t2 : t1;
-                const bool r1 = step<NAN_AWARE>(a, xc[(a.y & kFeatMask) * XS]) != (a.y >> kChildShift);
+                const bool r1 = goes_right<NAN_AWARE, false>(a, xa.get(a.y, i));
                 const uint2 lo = r1 ? t4 : t3, hi = r1 ? t6 : t5;
                 const uint2 b = r0 ? hi : lo;
-                pos[k][i] = step<NAN_AWARE>(b, xc[(b.y & kFeatMask) * XS]);
+                const uint32_t base = goes_right<NAN_AWARE, false>(b, xa.get(b.y, i)) ? nb8 : nb;
+                at[k][i] = base + Fmt::child_bytes(b.y);
             }
         }
         d0 = 3;
@@ -208,7 +269,7 @@ __device__ __forceinline__ void descend(const TreeView (&tv)[NT], const float* _
 #pragma unroll
         for (int k = 0; k < NT; ++k)
 #pragma unroll
-            for (int i = 0; i < SPT; ++i) pos[k][i] = 0u;
+            for (int i = 0; i < SPT; ++i) at[k][i] = tv[k].nodes;
     }
     int dmin = tv[0].depth, dmax = tv[0].depth;
 #pragma unroll
@@ -219,34 +280,42 @@ __device__ __forceinline__ void descend(const TreeView (&tv)[NT], const float* _
 #pragma unroll 2
     for (int d = d0; d < dmin; ++d) {
 #pragma unroll
-        for (int k = 0; k < NT; ++k)
+        for (int k = 0; k < NT; ++k) {
+            const uint32_t nb = tv[k].nodes, nb8 = nb + 8u;
 #pragma unroll
             for (int i = 0; i < SPT; ++i) {
-                const uint2 nd = tv[k].nodes[pos[k][i]];
-                pos[k][i] = step<NAN_AWARE>(nd, xcol[(nd.y & kFeatMask) * XS + i * STRIDE]);
+                const uint2 nd = lds64(at[k][i]);
+                const uint32_t base = goes_right<NAN_AWARE, false>(nd, xa.get(nd.y, i)) ? nb8 : nb;
+                at[k][i] = base + Fmt::child_bytes(nd.y);
             }
+        }
     }
     if (NT > 1) {
         for (int d = max(d0, dmin); d < dmax; ++d) {  // the deeper tree of the pair finishes alone
 #pragma unroll
             for (int k = 0; k < NT; ++k)
                 if (d < tv[k].depth) {
+                    const uint32_t nb = tv[k].nodes, nb8 = nb + 8u;
 #pragma unroll
                     for (int i = 0; i < SPT; ++i) {
-                        const uint2 nd = tv[k].nodes[pos[k][i]];
-                        pos[k][i] = step<NAN_AWARE>(nd, xcol[(nd.y & kFeatMask) * XS + i * STRIDE]);
+                        const uint2 nd = lds64(at[k][i]);
+                        const uint32_t base = goes_right<NAN_AWARE, false>(nd, xa.get(nd.y, i)) ? nb8 : nb;
+                        at[k][i] = base + Fmt::child_bytes(nd.y);
                     }
                 }
         }
     }
 #pragma unroll
-    for (int k = 0; k < NT; ++k)
+    for (int k = 0; k < NT; ++k) {
+        const uint32_t last = tv[k].nodes + tv[k].last_off;
+        const uint32_t vlast = tv[k].vals + tv[k].last_voff;
 #pragma unroll
         for (int i = 0; i < SPT; ++i) {
-            uint32_t v = pos[k][i] - tv[k].last_pos + tv[k].last_vidx;
-            if (pos[k][i] < tv[k].last_pos) v = tv[k].nodes[pos[k][i]].x;
-            vidx[k][i] = v;
+            uint32_t v = ((at[k][i] - last) << 1) + vlast;  // 8-byte slot -> 16-byte value
+            if (at[k][i] < last) v = tv[k].vals + (lds32(at[k][i]) << 4);
+            vaddr[k][i] = v;
         }
+    }
 }
 
 // =============================================================================== STREAM kernel
@@ -260,7 +329,7 @@ __device__ __forceinline__ void descend(const TreeView (&tv)[NT], const float* _
 // One warp moves 32 rows (lane = row) from a row-major chunk in shared memory into its own columns
 // of xs.  Row stride F floats: with 8-byte loads the 16 lanes of a half-warp hit 16 different bank
 // pairs (15*r mod 16 is a permutation), and the transposed stores are lane-consecutive.
-template <int XS>
+template <int FS>
 __device__ __forceinline__ bool transpose_group(float* __restrict__ xcol, const float* __restrict__ rows_rm, int F, int lane) {
     bool nan = false;
     const float* rp = rows_rm + lane * F;
@@ -269,14 +338,14 @@ __device__ __forceinline__ bool transpose_group(float* __restrict__ xcol, const 
 #pragma unroll 5
         for (int c2 = 0; c2 < (F >> 1); ++c2) {
             const float2 v = rp2[c2];
-            xcol[(2 * c2) * XS] = v.x;
-            xcol[(2 * c2 + 1) * XS] = v.y;
+            xcol[(2 * c2) * FS] = v.x;
+            xcol[(2 * c2 + 1) * FS] = v.y;
             nan |= (v.x != v.x) | (v.y != v.y);
         }
     } else {
         for (int c = 0; c < F; ++c) {
             const float v = rp[c];
-            xcol[c * XS] = v;
+            xcol[c * FS] = v;
             nan |= (v != v);
         }
     }
@@ -300,19 +369,32 @@ struct RingCursor {
     }
 };
 
-template <int SPT, int TPT, bool TOP>
+template <int SPT, int TPT, bool TOP, bool XB>
 __global__ void __launch_bounds__(kStreamThreads, 1)
-k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec_ok, const typename std::conditional<TOP, TopTable, NoTop>::type top) {
+k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const int vec_ok, const typename std::conditional<TOP, TopTable, NoTop>::type top) {
     constexpr int S = kConsumerThreads * SPT;
     constexpr int XS = S;
+    constexpr int FS = XB ? kBlockRows : XS;  // feature stride of xs in floats
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + kMaxStages;
-    float* xs = reinterpret_cast<float*>(smem + 128);
     const int F = f.n_features;
     const int T = f.n_trees;
     const uint32_t stage_bytes = f.stage_bytes;
-    uint8_t* ring = smem + 128 + round_up((uint32_t)(F + 1) * XS * 4u, 128u);
+    // blocked rows start on an 8 KB boundary of the shared window (XBlocked); what the padding
+    // costs comes out of the ring
+    uint32_t xs_off = 128u, xs_bytes = round_up((uint32_t)(F + 1) * XS * 4u, 128u);
+    int n_stages = n_stages_planned;
+    if (XB) {
+        const uint32_t base = smem_u32(smem);
+        xs_off = ((base + 128u + kBlockBytes - 1u) & ~(kBlockBytes - 1u)) - base;
+        xs_bytes = (uint32_t)(S / kBlockRows) * kBlockBytes;
+        uint32_t total;
+        asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(total));
+        n_stages = min(n_stages, (int)((total - xs_off - xs_bytes) / stage_bytes));
+    }
+    float* xs = reinterpret_cast<float*>(smem + xs_off);
+    uint8_t* ring = smem + xs_off + xs_bytes;
     const int tid = threadIdx.x;
     const int64_t n_batches = (a.n + S - 1) / S;
     const int R = (int)f.chunk_rows;  // rows per row chunk, a multiple of 32
@@ -325,7 +407,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
         }
         mbar_fence_init();
     }
-    for (int i = tid; i < XS; i += kStreamThreads) xs[F * XS + i] = 0.0f;
+    for (int i = tid; i < S; i += kStreamThreads) xs[(XB ? blocked_row(i) : i) + F * FS] = 0.0f;
     __syncthreads();
 
     if (tid >= kConsumerThreads) {
@@ -361,6 +443,13 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
     // ---- consumers
     const int lane = tid & 31, warp = tid >> 5;
     const double Td = (double)T;
+    typename std::conditional<XB, XBlocked<kConsumerThreads>, XStrided<kConsumerThreads>>::type xa;
+    if constexpr (XB)
+        xa.tb = smem_u32(xs) + (uint32_t)blocked_row(tid) * 4u;
+    else {
+        xa.xcol = xs + tid;
+        xa.XS = XS;
+    }
     RingCursor acq, rel;  // next stage to wait for / oldest stage this warp still holds
     for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
         const int64_t row0 = b * S;
@@ -376,7 +465,8 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
                 const float* chunk = reinterpret_cast<const float*>(ring + (size_t)acq.stage * stage_bytes);
                 for (int lg = (warp - c * k) & (kConsumerWarps - 1); lg < cnt; lg += kConsumerWarps) {
                     const int i = (c * k + lg) / kConsumerWarps;  // which of this thread's SPT rows
-                    my_nan |= transpose_group<XS>(xs + tid + i * kConsumerThreads, chunk + (size_t)lg * 32 * F, F, lane);
+                    const int s = tid + i * kConsumerThreads;
+                    my_nan |= transpose_group<FS>(xs + (XB ? blocked_row(s) : s), chunk + (size_t)lg * 32 * F, F, lane);
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(empty + acq.stage);
@@ -387,7 +477,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
         } else {
             // ragged last batch, strided or unaligned rows: cooperative load with block barriers
             named_bar_sync(1, kConsumerThreads);
-            const bool my_nan = load_tile<kConsumerThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+            const bool my_nan = load_tile<kConsumerThreads, S, XB>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
             any_nan = named_bar_or(2, kConsumerThreads, my_nan);
         }
 
@@ -411,17 +501,17 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
                     rel_off = tp.rel_off;
                     values_off = tp.values_off;
                     depth_flags = tp.depth_flags;
-                    tv[k].last_pos = tp.last_pos;
-                    tv[k].last_vidx = tp.last_vidx;
+                    tv[k].last_off = tp.last_pos << 3;
+                    tv[k].last_voff = tp.last_vidx << 4;
                     tv[k].top = reinterpret_cast<const uint2*>(tp.top.n);
                 } else {
                     const int4 raw = __ldg(reinterpret_cast<const int4*>(f.trees + t));      // TreeRec, first half
                     const int4 raw2 = __ldg(reinterpret_cast<const int4*>(f.trees + t) + 1);  // second half
                     rel_off = (uint32_t)raw2.z;
                     values_off = (uint32_t)raw.z;
-                    depth_flags = (uint32_t)raw.w | ((uint32_t)raw2.w << 16);
-                    tv[k].last_pos = (uint32_t)raw2.x;
-                    tv[k].last_vidx = (uint32_t)raw2.y;
+                    depth_flags = (uint32_t)raw.w | (((uint32_t)raw2.w & 3u) << 16);
+                    tv[k].last_off = (uint32_t)raw2.x << 3;
+                    tv[k].last_voff = (uint32_t)raw2.y << 4;
                     tv[k].top = nullptr;
                 }
                 if (valid && (depth_flags & 0x10000u)) {  // first tree of a group: its stage must have landed
@@ -430,33 +520,33 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages, const int vec
                     acq.advance(n_stages);
                 }
                 const uint8_t* tb = gb + rel_off;
-                tv[k].nodes = reinterpret_cast<const uint2*>(tb);
-                tv[k].vals = reinterpret_cast<const double2*>(tb + values_off);
+                tv[k].nodes = smem_u32(tb);
+                tv[k].vals = tv[k].nodes + values_off;
                 tv[k].depth = (int)(depth_flags & 0xFFFFu);
                 last_of_group[k] = valid && (depth_flags & 0x20000u);
             }
-            uint32_t vidx[TPT][SPT];
+            uint32_t voff[TPT][SPT];
             if (TPT == 1 || t0 + TPT <= T) {
                 if (!any_nan)
-                    descend<SPT, TPT, kConsumerThreads, false, TOP>(tv, xs + tid, XS, vidx);
+                    descend<SPT, TPT, false, TOP>(tv, xa, voff);
                 else
-                    descend<SPT, TPT, kConsumerThreads, true, TOP>(tv, xs + tid, XS, vidx);
+                    descend<SPT, TPT, true, TOP>(tv, xa, voff);
             } else {
                 TreeView one[1] = {tv[0]};
                 uint32_t v1[1][SPT];
                 if (!any_nan)
-                    descend<SPT, 1, kConsumerThreads, false, TOP>(one, xs + tid, XS, v1);
+                    descend<SPT, 1, false, TOP>(one, xa, v1);
                 else
-                    descend<SPT, 1, kConsumerThreads, true, TOP>(one, xs + tid, XS, v1);
+                    descend<SPT, 1, true, TOP>(one, xa, v1);
 #pragma unroll
-                for (int i = 0; i < SPT; ++i) vidx[0][i] = v1[0][i];
+                for (int i = 0; i < SPT; ++i) voff[0][i] = v1[0][i];
             }
 #pragma unroll
             for (int k = 0; k < TPT; ++k) {
                 if (t0 + k < T) {
 #pragma unroll
                     for (int i = 0; i < SPT; ++i) {
-                        const double2 v = tv[k].vals[vidx[k][i]];
+                        const double2 v = lds128d(voff[k][i]);
                         acc0[i] += v.x;  // tree order, plain adds: SK/ensemble/_forest.py:714
                         acc1[i] += v.y;
                     }
@@ -497,7 +587,7 @@ struct GlobalTree {
 };
 
 // NT trees walked together by each thread: NT independent chains of dependent L2/HBM loads in flight.
-template <int NT, bool NAN_AWARE>
+template <int NT, bool NAN_AWARE, bool WIDE>
 __device__ __forceinline__ void descend_global(const GlobalTree (&gt)[NT], const float* __restrict__ xcol, int XS, uint32_t leaf_feat, uint32_t (&vidx)[NT]) {
     uint32_t pos[NT];
     int dmax = 0;
@@ -510,10 +600,12 @@ __device__ __forceinline__ void descend_global(const GlobalTree (&gt)[NT], const
         bool all_leaf = true;
 #pragma unroll
         for (int k = 0; k < NT; ++k) {
-            uint2 nd = make_uint2(0u, (pos[k] << kChildShift) | leaf_feat);  // synthetic self-looping leaf
+            using Fmt = NodeFmt<WIDE>;
+            uint2 nd = make_uint2(0u, Fmt::make(pos[k], false, leaf_feat));  // synthetic self-looping leaf
             if (d < gt[k].depth && pos[k] < gt[k].last_pos) nd = __ldg(gt[k].nodes + pos[k]);
-            pos[k] = step<NAN_AWARE>(nd, xcol[(nd.y & kFeatMask) * XS]);
-            all_leaf = all_leaf && ((nd.y & kFeatMask) == leaf_feat);
+            const uint32_t feat = Fmt::feature(nd.y);
+            pos[k] = Fmt::child(nd.y) + (goes_right<NAN_AWARE, WIDE>(nd, xcol[feat * XS]) ? 1u : 0u);
+            all_leaf = all_leaf && (feat == leaf_feat);
         }
         if ((d & 3) == 3 && __all_sync(0xffffffffu, all_leaf)) break;
     }
@@ -528,7 +620,7 @@ __device__ __forceinline__ void descend_global(const GlobalTree (&gt)[NT], const
 // kGlobalTrees trees per thread at a time: two independent chains of dependent loads per thread.
 // (Measured on unbounded-depth forests with the L1 carve-out below: 1 tree 12.1 ms, 2 trees 9.1 ms,
 // 4 trees 10.8 ms per 2 M rows x 100 trees.)
-template <int kGlobalTrees, int kGlobalThreads>
+template <int kGlobalTrees, int kGlobalThreads, bool WIDE>
 __global__ void __launch_bounds__(kGlobalThreads) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
     constexpr int S = kGlobalThreads, XS = S;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -557,9 +649,9 @@ __global__ void __launch_bounds__(kGlobalThreads) k_global(const ForestDev f, co
         }
         uint32_t vidx[kGlobalTrees];
         if (any_nan)
-            descend_global<kGlobalTrees, true>(gt, xs + tid, XS, (uint32_t)F, vidx);
+            descend_global<kGlobalTrees, true, WIDE>(gt, xs + tid, XS, (uint32_t)F, vidx);
         else
-            descend_global<kGlobalTrees, false>(gt, xs + tid, XS, (uint32_t)F, vidx);
+            descend_global<kGlobalTrees, false, WIDE>(gt, xs + tid, XS, (uint32_t)F, vidx);
 #pragma unroll
         for (int k = 0; k < kGlobalTrees; ++k) {
             if (t0 + k < T) {
@@ -614,18 +706,19 @@ __global__ void __launch_bounds__(kTileThreads) k_split_descend(const ForestDev 
         mbar_wait(full + stage, phase);
         const uint8_t* tb = ring + (size_t)stage * stage_bytes;
         TreeView tv[1];
-        tv[0].nodes = reinterpret_cast<const uint2*>(tb);
-        tv[0].vals = reinterpret_cast<const double2*>(tb + (uint32_t)raw.z);
+        tv[0].nodes = smem_u32(tb);
+        tv[0].vals = tv[0].nodes + (uint32_t)raw.z;
         tv[0].top = nullptr;
         tv[0].depth = raw.w;
-        tv[0].last_pos = (uint32_t)raw2.x;
-        tv[0].last_vidx = (uint32_t)raw2.y;
-        uint32_t vidx[1][1];
+        tv[0].last_off = (uint32_t)raw2.x << 3;
+        tv[0].last_voff = (uint32_t)raw2.y << 4;
+        uint32_t voff[1][1];
+        const XStrided<0> xa{xs + tid, XS};
         if (!any_nan)
-            descend<1, 1, 0, false, false>(tv, xs + tid, XS, vidx);
+            descend<1, 1, false, false>(tv, xa, voff);
         else
-            descend<1, 1, 0, true, false>(tv, xs + tid, XS, vidx);
-        const double2 v = tv[0].vals[vidx[0][0]];
+            descend<1, 1, true, false>(tv, xa, voff);
+        const double2 v = lds128d(voff[0][0]);
         if (tid < rows) scratch[(int64_t)t * a.n + row0 + tid] = v;
         const int t_next = t + kSplitStages;
         if (t_next < t_hi) {
@@ -693,16 +786,24 @@ struct StreamPlan {
     uint32_t smem_bytes = 0;
 };
 
+// Rows in the blocked layout (one and-or per x address) whenever the features and the dummy row fit
+// a block's 32 feature rows.
+bool stream_blocked(const ccfd_forest* f) { return f->dev.n_features <= kMaxBlockedFeatures; }
+
 StreamPlan plan_stream(const ccfd_forest* f, int spt) {
     StreamPlan p;
     const uint32_t S = kConsumerThreads * spt;
-    const uint32_t xs_bytes = round_up((uint32_t)(f->dev.n_features + 1) * S * 4u, 128u);
+    const bool xb = stream_blocked(f);
+    // blocked: the rows start on an 8 KB boundary of the shared window; the kernel finds out where that
+    // is, the plan assumes the worst case and asks for all the shared memory there is
+    const uint32_t xs_bytes = xb ? (S / kBlockRows) * kBlockBytes : round_up((uint32_t)(f->dev.n_features + 1) * S * 4u, 128u);
+    const uint32_t head = xb ? 128u + kBlockBytes : 128u;
     p.stage_bytes = f->dev.stage_bytes;
-    const int64_t budget = (int64_t)f->smem_optin - 128 - (int64_t)xs_bytes;
+    const int64_t budget = (int64_t)f->smem_optin - (int64_t)head - (int64_t)xs_bytes;
     if (budget < 2 * (int64_t)p.stage_bytes) return p;
     p.n_stages = (int)(budget / p.stage_bytes);
     if (p.n_stages > kMaxStages) p.n_stages = kMaxStages;
-    p.smem_bytes = 128 + xs_bytes + (uint32_t)p.n_stages * p.stage_bytes;
+    p.smem_bytes = xb ? (uint32_t)f->smem_optin : 128 + xs_bytes + (uint32_t)p.n_stages * p.stage_bytes;
     p.ok = true;
     return p;
 }
@@ -726,14 +827,16 @@ int ccfd_kernels_init(ccfd_forest* f) {
     int major = 0;
     CCFD_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, f->device));
     if (major != 10) return ccfd_fail(CCFD_EUNSUPPORTED, "libccfd_rf is built for sm_100a (B200); device %d has compute capability major %d", f->device, major);
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+#define CCFD_STREAM_ATTRS(SPT_, TPT_)                                                                                                       \
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<SPT_, TPT_, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin)); \
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<SPT_, TPT_, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));  \
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<SPT_, TPT_, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));  \
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<SPT_, TPT_, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_STREAM_ATTRS(1, 1)
+    CCFD_STREAM_ATTRS(2, 1)
+    CCFD_STREAM_ATTRS(1, 2)
+    CCFD_STREAM_ATTRS(2, 2)
+#undef CCFD_STREAM_ATTRS
     CCFD_CUDA(cudaFuncSetAttribute(k_split_descend, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     {
         // GLOBAL walks nodes through L1/L2: leave most of the SM's 256 KB to L1 so that the upper levels
@@ -741,9 +844,11 @@ int ccfd_kernels_init(ccfd_forest* f) {
         // 2 M rows, 256-thread CTAs: default carve-out 25.0 ms, 40 % 9.1 ms, 60 % 12.1 ms.
         int carveout = 40;
         if (const char* e = getenv("CCFD_GLOBAL_CARVEOUT")) carveout = atoi(e);  // tuning knob
-#define CCFD_GLOBAL_ATTRS(NT_, TH_)                                                                                          \
-    CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin)); \
-    CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
+#define CCFD_GLOBAL_ATTRS(NT_, TH_)                                                                                                 \
+    CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));  \
+    CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));    \
+    CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));   \
+    CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
         CCFD_GLOBAL_ATTRS(1, kGlobalThreadsBulk)
         CCFD_GLOBAL_ATTRS(2, kGlobalThreadsBulk)
         CCFD_GLOBAL_ATTRS(1, kGlobalThreadsSmall)
@@ -759,7 +864,8 @@ int ccfd_kernels_init(ccfd_forest* f) {
     f->dev.chunk_rows = f->dev.stage_bytes / (F * 4u) / 32u * 32u;
     f->dev.groups = nullptr;
     f->dev.n_groups = 0;
-    f->info.stream_kernel_ok = (plan_stream(f, 1).ok && split_ok(f, nullptr)) ? 1 : 0;
+    f->dev.wide_nodes = (f->host_trees[0].group_flags & kWideNodesFlag) ? 1u : 0u;
+    f->info.stream_kernel_ok = (!f->dev.wide_nodes && plan_stream(f, 1).ok && split_ok(f, nullptr)) ? 1 : 0;
     if (f->info.stream_kernel_ok) {
         std::vector<GroupRec> groups;
         for (int t = 0; t < f->dev.n_trees; ++t) {
@@ -794,7 +900,7 @@ int ccfd_kernels_init(ccfd_forest* f) {
                 tp.top = f->host_top[(size_t)t];
                 tp.rel_off = tr.rel_off;
                 tp.values_off = tr.values_off;
-                tp.depth_flags = tr.depth | (tr.group_flags << 16);
+                tp.depth_flags = tr.depth | ((tr.group_flags & 3u) << 16);
                 tp.last_pos = tr.last_pos;
                 tp.last_vidx = tr.last_vidx;
                 tp.pad = 0;
@@ -839,21 +945,28 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         bool use_top = !f->host_params.empty();
         if (const char* e = getenv("CCFD_STREAM_TPT")) tpt = atoi(e) == 2 ? 2 : 1;   // tuning knobs for experiments
         if (const char* e = getenv("CCFD_STREAM_TOP")) use_top = use_top && atoi(e) != 0;
-#define CCFD_LAUNCH_STREAM(SPT_, TPT_)                                                                                            \
-    do {                                                                                                                          \
-        if (use_top) {                                                                                                            \
-            static_assert(sizeof(TopTable) + 256 < 32764, "kernel parameter space");                                              \
-            TopTable top; /* per-tree metadata and top three levels travel as kernel parameters (constant bank) */                 \
-            memcpy(top.t, f->host_params.data(), sizeof(TreeParam) * f->host_params.size());                                      \
-            k_stream<SPT_, TPT_, true><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok, top);        \
-        } else {                                                                                                                  \
-            k_stream<SPT_, TPT_, false><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok, NoTop{});   \
-        }                                                                                                                         \
+        const bool xb = stream_blocked(f);
+#define CCFD_LAUNCH_STREAM_X(SPT_, TPT_, XB_)                                                                                            \
+    do {                                                                                                                                 \
+        if (use_top) {                                                                                                                   \
+            static_assert(sizeof(TopTable) + 256 < 32764, "kernel parameter space");                                                     \
+            TopTable top; /* per-tree metadata and top three levels travel as kernel parameters (constant bank) */                        \
+            memcpy(top.t, f->host_params.data(), sizeof(TreeParam) * f->host_params.size());                                             \
+            k_stream<SPT_, TPT_, true, XB_><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok, top);          \
+        } else {                                                                                                                         \
+            k_stream<SPT_, TPT_, false, XB_><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, vec_ok, NoTop{});     \
+        }                                                                                                                                \
+    } while (0)
+#define CCFD_LAUNCH_STREAM(SPT_, TPT_)                 \
+    do {                                               \
+        if (xb) CCFD_LAUNCH_STREAM_X(SPT_, TPT_, true); \
+        else CCFD_LAUNCH_STREAM_X(SPT_, TPT_, false);   \
     } while (0)
         if (spt == 2 && tpt == 2) CCFD_LAUNCH_STREAM(2, 2);
         else if (spt == 2) CCFD_LAUNCH_STREAM(2, 1);
         else if (tpt == 2) CCFD_LAUNCH_STREAM(1, 2);
         else CCFD_LAUNCH_STREAM(1, 1);
+#undef CCFD_LAUNCH_STREAM_X
 #undef CCFD_LAUNCH_STREAM
     } else if (kernel == CCFD_KERNEL_SPLIT) {
         uint32_t smem_bytes = 0;
@@ -897,10 +1010,13 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         const uint32_t gsmem = xs_bytes(threads);
         int nt = 2;
         if (const char* e = getenv("CCFD_GLOBAL_NT")) nt = atoi(e);  // tuning knob
+        const bool wide = f->dev.wide_nodes != 0;
 #define CCFD_LAUNCH_GLOBAL(TH_)                                                                        \
     do {                                                                                               \
-        if (nt == 2) k_global<2, TH_><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);     \
-        else k_global<1, TH_><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);             \
+        if (nt == 2 && wide) k_global<2, TH_, true><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);        \
+        else if (nt == 2) k_global<2, TH_, false><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);          \
+        else if (wide) k_global<1, TH_, true><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);              \
+        else k_global<1, TH_, false><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);                       \
     } while (0)
         if (threads == kGlobalThreadsBulk) CCFD_LAUNCH_GLOBAL(kGlobalThreadsBulk);
         else if (threads == kGlobalThreadsSmall) CCFD_LAUNCH_GLOBAL(kGlobalThreadsSmall);

@@ -1,5 +1,5 @@
 """Test helper: numpy walk over the *packed* forest image exactly as the CUDA kernels walk it
-(csrc/kernels.cu `step` / `descend_smem`): float32 compare, sibling-pair child slot, self-looping
+(csrc/kernels.cu `goes_right` / `descend`): float32 compare, sibling-pair child slot, self-looping
 leaves reading the all-zero dummy feature, fixed trip count = tree depth, float64 sums in tree
 order, true divide.  Lets the CPU suite check converter + re-layout + bit packing without a GPU."""
 import ctypes
@@ -31,17 +31,49 @@ def pack(fa):
     return blob, recs, top
 
 
-def _step(thr_bits, meta, x):
+class _Fmt:
+    """Field access for the two node encodings (csrc/ccfd_internal.h NodeFmt): compact for forests
+    whose trees fit shared memory, wide for the rest (TreeRec.group_flags bit 2)."""
+
+    def __init__(self, wide):
+        self.wide = bool(wide)
+
+    def feature(self, meta):
+        return (meta & 0xFF) if self.wide else ((meta >> 8) & 0xFF)
+
+    def mgl(self, meta):
+        return ((meta & 0x100) != 0) if self.wide else ((meta & 1) != 0)
+
+    def child(self, meta):  # in node slots
+        if self.wide:
+            return (meta >> 9).astype(np.int64) if isinstance(meta, np.ndarray) else int(meta) >> 9
+        off = meta >> 16
+        assert np.all(off % 8 == 0), "compact child reference is a byte offset of an 8-byte slot"
+        return (off // 8).astype(np.int64) if isinstance(off, np.ndarray) else int(off) // 8
+
+
+def fmt_of(recs):
+    wide = (recs[:, 7] & 4) != 0
+    assert wide.all() or not wide.any(), "one encoding per forest"
+    return _Fmt(wide.any())
+
+
+def _right(fmt, thr_bits, meta, x):
     with np.errstate(invalid="ignore"):
         left = x <= thr_bits.view(np.float32)
-    left = np.where(np.isnan(x), (meta & 0x100) != 0, left)
-    return (meta >> 9).astype(np.int64) + np.where(left, 0, 1)
+    left = np.where(np.isnan(x), fmt.mgl(meta), left)
+    return ~left
+
+
+def _step(fmt, thr_bits, meta, x):
+    return fmt.child(meta) + _right(fmt, thr_bits, meta, x).astype(np.int64)
 
 
 def predict_proba(blob, recs, n_features, X32, top=None):
     """top=None: every level from the node array.  top given: the first three levels from the
-    seven-node table, picked with selects, as the STREAM kernel does (descend_smem<TOP=true>)."""
+    seven-node table, picked with selects, as the STREAM kernel does (descend<TOP=true>)."""
     n = X32.shape[0]
+    fmt = fmt_of(recs)
     xs = np.concatenate([X32, np.zeros((n, 1), np.float32)], axis=1)  # dummy feature row = 0
     acc = np.zeros((n, 2), dtype=np.float64)
     rows = np.arange(n)
@@ -56,20 +88,20 @@ def predict_proba(blob, recs, n_features, X32, top=None):
             tp = top[t]
             pick = lambda idx: (tp[idx, 0], tp[idx, 1])  # noqa: E731
             tb0, m0 = tp[0]
-            r0 = _step(np.full(n, tb0, np.uint32), np.full(n, m0, np.uint32), xs[rows, m0 & 0xFF]) != (m0 >> 9)
+            r0 = _right(fmt, np.full(n, tb0, np.uint32), np.full(n, m0, np.uint32), xs[rows, fmt.feature(m0)])
             tb1, m1 = pick(np.where(r0, 2, 1))
-            r1 = _step(tb1, m1, xs[rows, m1 & 0xFF]) != (m1 >> 9)
+            r1 = _right(fmt, tb1, m1, xs[rows, fmt.feature(m1)])
             tb2, m2 = pick(3 + 2 * r0.astype(np.int64) + r1.astype(np.int64))
-            pos, d0 = _step(tb2, m2, xs[rows, m2 & 0xFF]), 3
+            pos, d0 = _step(fmt, tb2, m2, xs[rows, fmt.feature(m2)]), 3
         last_pos = int(last_pos)
         assert nodes.shape[0] in (last_pos, last_pos + 1), "node array = slots above the deepest level (+ pad)"
         for _ in range(d0, int(depth)):
             assert np.all(pos < last_pos), "a stored slot is read on every step"
             m = meta[pos]
-            pos = _step(thr_bits[pos], m, xs[rows, m & 0xFF])
+            pos = _step(fmt, thr_bits[pos], m, xs[rows, fmt.feature(m)])
         # rows on the deepest level compute their value index, the rest read their leaf slot
         shallow = pos < last_pos
-        assert np.all((meta[pos[shallow]] & 0xFF) == n_features), "descent did not end on a leaf"
+        assert np.all(fmt.feature(meta[pos[shallow]]) == n_features), "descent did not end on a leaf"
         vidx = pos - last_pos + int(last_vidx)
         vidx[shallow] = thr_bits[pos[shallow]]
         assert vidx.min() >= 0 and vidx.max() < len(vals)

@@ -61,12 +61,14 @@ def test_pack_layout_invariants():
         # slots of the deepest level (leaves only) are not stored
         assert int(values_off) == (int(last_pos) * 8 + 15) // 16 * 16
         nodes = blob[int(off16) * 16: int(off16) * 16 + int(last_pos) * 8].view(np.uint32).reshape(-1, 2)
-        internal = (nodes[:, 1] & 0xFF) != fa.n_features
-        child = nodes[internal, 1] >> 9
+        fmt = packed_emulator.fmt_of(recs)
+        assert not fmt.wide  # trees this small use the compact encoding: byte offsets, feature << 8, mgl bit 0
+        internal = fmt.feature(nodes[:, 1]) != fa.n_features
+        child = fmt.child(nodes[internal, 1])
         # siblings adjacent, children after parents, every slot referenced exactly once
         assert np.array_equal(np.sort(np.concatenate([child, child + 1])), np.arange(1, n_src))
         assert np.all(child > np.nonzero(internal)[0])
-        assert np.array_equal(nodes[~internal, 1] >> 9, np.nonzero(~internal)[0])  # leaves point at themselves
+        assert np.array_equal(fmt.child(nodes[~internal, 1]), np.nonzero(~internal)[0])  # leaves point at themselves
         assert n_src - int(last_pos) == n_leaves - int(last_vidx)  # deepest level: consecutive value indices to the end
 
 
