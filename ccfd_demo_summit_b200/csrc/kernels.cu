@@ -277,7 +277,7 @@ __device__ __forceinline__ void descend(const TreeView (&tv)[NT], const XA xa, u
         dmin = min(dmin, tv[k].depth);
         dmax = max(dmax, tv[k].depth);
     }
-#pragma unroll 2
+#pragma unroll 1  // measured: unroll 1 / 2 / 4 = 7.13 / 7.23 / 7.18 ms (hard), 5.21 / 5.32 / 5.36 ms (easy) per 12.5 M rows
     for (int d = d0; d < dmin; ++d) {
 #pragma unroll
         for (int k = 0; k < NT; ++k) {
@@ -672,13 +672,21 @@ __global__ void __launch_bounds__(kGlobalThreads) k_global(const ForestDev f, co
 // ================================================================================ SPLIT kernels
 // grid.x = 256-row tiles, grid.y = tree chunks.  Each CTA brings its chunk's trees into a 2-stage
 // shared-memory ring by TMA and writes scratch[t][row] = (v0, v1) of the leaf row lands in.
+template <bool XB>
 __global__ void __launch_bounds__(kTileThreads) k_split_descend(const ForestDev f, const ScoreArgs a, double2* __restrict__ scratch, const int trees_per_cta, const uint32_t stage_bytes, const int vec_ok) {
     constexpr int S = kTileThreads, XS = S;
+    constexpr int FS = XB ? kBlockRows : XS;
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-    float* xs = reinterpret_cast<float*>(smem + 128);
     const int F = f.n_features, tid = threadIdx.x;
-    uint8_t* ring = smem + 128 + round_up((uint32_t)(F + 1) * XS * 4u, 128u);
+    uint32_t xs_off = 128u, xs_bytes = round_up((uint32_t)(F + 1) * XS * 4u, 128u);
+    if (XB) {  // blocked rows start on an 8 KB boundary of the shared window; the host sized for the worst case
+        const uint32_t base = smem_u32(smem);
+        xs_off = ((base + 128u + kBlockBytes - 1u) & ~(kBlockBytes - 1u)) - base;
+        xs_bytes = (uint32_t)(S / kBlockRows) * kBlockBytes;
+    }
+    float* xs = reinterpret_cast<float*>(smem + xs_off);
+    uint8_t* ring = smem + xs_off + xs_bytes;
     const int t_lo = blockIdx.y * trees_per_cta;
     const int t_hi = min(f.n_trees, t_lo + trees_per_cta);
     const int64_t row0 = (int64_t)blockIdx.x * S;
@@ -694,9 +702,16 @@ __global__ void __launch_bounds__(kTileThreads) k_split_descend(const ForestDev 
             bulk_g2s(ring + (size_t)s * stage_bytes, f.blob + (size_t)tr.blob_off16 * 16u, tr.blob_bytes, full + s);
         }
     }
-    for (int i = tid; i < XS; i += kTileThreads) xs[F * XS + i] = 0.0f;
-    const bool my_nan = load_tile<kTileThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+    for (int i = tid; i < S; i += kTileThreads) xs[(XB ? blocked_row(i) : i) + F * FS] = 0.0f;
+    const bool my_nan = load_tile<kTileThreads, S, XB>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
     const bool any_nan = __syncthreads_or(my_nan) != 0;  // also publishes the mbarrier inits
+    typename std::conditional<XB, XBlocked<kBlockRows>, XStrided<0>>::type xa;
+    if constexpr (XB)
+        xa.tb = smem_u32(xs) + (uint32_t)blocked_row(tid) * 4u;
+    else {
+        xa.xcol = xs + tid;
+        xa.XS = XS;
+    }
 
     int stage = 0;
     uint32_t phase = 0;
@@ -713,7 +728,6 @@ __global__ void __launch_bounds__(kTileThreads) k_split_descend(const ForestDev 
         tv[0].last_off = (uint32_t)raw2.x << 3;
         tv[0].last_voff = (uint32_t)raw2.y << 4;
         uint32_t voff[1][1];
-        const XStrided<0> xa{xs + tid, XS};
         if (!any_nan)
             descend<1, 1, false, false>(tv, xa, voff);
         else
@@ -788,7 +802,10 @@ struct StreamPlan {
 
 // Rows in the blocked layout (one and-or per x address) whenever the features and the dummy row fit
 // a block's 32 feature rows.
-bool stream_blocked(const ccfd_forest* f) { return f->dev.n_features <= kMaxBlockedFeatures; }
+bool stream_blocked(const ccfd_forest* f) {
+    static const bool off = getenv("CCFD_NO_BLOCKED_ROWS") != nullptr;  // tuning knob for A/B runs
+    return !off && f->dev.n_features <= kMaxBlockedFeatures;
+}
 
 StreamPlan plan_stream(const ccfd_forest* f, int spt) {
     StreamPlan p;
@@ -808,11 +825,15 @@ StreamPlan plan_stream(const ccfd_forest* f, int spt) {
     return p;
 }
 
-uint32_t tile_xs_bytes(const ccfd_forest* f) { return round_up((uint32_t)(f->dev.n_features + 1) * kTileThreads * 4u, 128u); }
+// SPLIT tile: rows (blocked layout: worst-case padding to the next 8 KB boundary included)
+uint32_t tile_xs_bytes(const ccfd_forest* f, bool blocked) {
+    if (blocked) return kBlockBytes + (kTileThreads / kBlockRows) * kBlockBytes;
+    return round_up((uint32_t)(f->dev.n_features + 1) * kTileThreads * 4u, 128u);
+}
 
-bool split_ok(const ccfd_forest* f, uint32_t* smem_bytes) {
+bool split_ok(const ccfd_forest* f, uint32_t* smem_bytes, bool blocked = false) {
     const uint32_t stage = round_up(f->dev.max_tree_bytes, 128u);
-    const uint32_t need = 128 + tile_xs_bytes(f) + kSplitStages * stage;
+    const uint32_t need = 128 + tile_xs_bytes(f, blocked) + kSplitStages * stage;
     if (smem_bytes) *smem_bytes = need;
     // keep it small enough for 2 CTAs per SM so short requests overlap
     return need <= (uint32_t)f->smem_optin / 2;
@@ -837,7 +858,8 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_STREAM_ATTRS(1, 2)
     CCFD_STREAM_ATTRS(2, 2)
 #undef CCFD_STREAM_ATTRS
-    CCFD_CUDA(cudaFuncSetAttribute(k_split_descend, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_split_descend<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_CUDA(cudaFuncSetAttribute(k_split_descend<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     {
         // GLOBAL walks nodes through L1/L2: leave most of the SM's 256 KB to L1 so that the upper levels
         // of the trees the resident CTAs are on stay in L1.  Measured on a 100-tree unbounded forest,
@@ -969,7 +991,7 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
 #undef CCFD_LAUNCH_STREAM_X
 #undef CCFD_LAUNCH_STREAM
     } else if (kernel == CCFD_KERNEL_SPLIT) {
-        uint32_t smem_bytes = 0;
+        uint32_t smem_bytes = 0, smem_blocked = 0;
         if (!split_ok(f, &smem_bytes) || !f->info.stream_kernel_ok) return ccfd_fail(CCFD_EUNSUPPORTED, "largest tree (%u bytes) does not fit the shared-memory ring of the SPLIT kernel", f->dev.max_tree_bytes);
         if (!scratch) return ccfd_fail(CCFD_EINVAL, "SPLIT kernel needs scratch");
         const int64_t tiles = (a.n + kTileThreads - 1) / kTileThreads;
@@ -983,7 +1005,13 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         if (chunks > 65535) return ccfd_fail(CCFD_EINVAL, "too many tree chunks");
         const uint32_t stage_bytes = round_up(f->dev.max_tree_bytes, 128u);
         dim3 grid((unsigned)tiles, (unsigned)chunks);
-        k_split_descend<<<grid, kTileThreads, smem_bytes, stream>>>(f->dev, a, static_cast<double2*>(scratch), trees_per_cta, stage_bytes, vec_ok);
+        // The blocked row layout saves instructions on every level but its padding to an 8 KB boundary
+        // costs the third resident CTA per SM: use it when the grid fits two CTAs per SM anyway
+        // (1,024 rows: 23.6 -> 22.1 us; 16,384 rows, 320 CTAs: 39 us strided, 54 us blocked).
+        if (stream_blocked(f) && tiles * chunks <= 2 * (int64_t)f->sm_count && split_ok(f, &smem_blocked, true))
+            k_split_descend<true><<<grid, kTileThreads, smem_blocked, stream>>>(f->dev, a, static_cast<double2*>(scratch), trees_per_cta, stage_bytes, vec_ok);
+        else
+            k_split_descend<false><<<grid, kTileThreads, smem_bytes, stream>>>(f->dev, a, static_cast<double2*>(scratch), trees_per_cta, stage_bytes, vec_ok);
         {
             // Programmatic dependent launch: the reduce grid may be scheduled while the descent drains and
             // waits in cudaGridDependencySynchronize() for the descent's memory to be visible, which takes
