@@ -56,3 +56,36 @@ def test_cuda_kernels_equal_oracle_on_random_forests(seed, n_trees, max_internal
     got = forest.predict_proba(X)  # host pointers, kernel picked by the library
     assert np.array_equal(bits(got), bits(want))
     forest.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("F", [31, 32])
+@pytest.mark.parametrize("with_nan", [False, True])
+def test_row_layout_boundary(F, with_nan):
+    """31 features is the last count that takes the blocked shared-memory row layout (64-row blocks of
+    32 feature rows, the x address one and-or of the node's meta word), 32 the first that takes the
+    strided one.  Every way rows reach shared memory is exercised on both sides: TMA row chunks
+    (dense, aligned), the cooperative loader (ragged last batch, strided or unaligned rows), one and
+    two rows per thread, and the SPLIT tiles in both of their layouts."""
+    import torch
+
+    from ccfd_demo_summit_b200 import model
+
+    raw = rfs.random_forest(100 + F, 9, 400, F, 0.4)
+    n = 160_000 + 77  # two rows per thread in STREAM, with a ragged last batch
+    X = rfs.random_rows(F, raw, n)
+    if not with_nan:
+        X = np.nan_to_num(X, nan=0.25)
+    want = rf_oracle.predict_proba_c(raw, X)
+    forest = model.Forest(_fa(raw))
+    assert forest.info["stream_kernel_ok"]
+    st_ = torch.cuda.current_stream().cuda_stream
+    for ld, off in [(F, 0), (F + 3, 0), (F, 1)]:
+        buf = torch.zeros(n * ld + 8, dtype=torch.float32, device="cuda")
+        xs = buf[off:off + n * ld].view(n, ld)
+        xs[:, :F] = torch.from_numpy(X).cuda()
+        for kernel, m in [("stream", n), ("stream", 20_000), ("stream", 513), ("split", 1024), ("split", 6000), ("split", 1), ("global", 3000)]:
+            out = torch.full((m, 2), -1.0, dtype=torch.float64, device="cuda")
+            forest.predict_proba_device(xs.data_ptr(), m, ld, out.data_ptr(), st_, kernel)
+            assert np.array_equal(bits(out.cpu().numpy()), bits(want[:m])), (kernel, m, ld, off)
+    forest.close()
