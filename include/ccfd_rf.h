@@ -94,7 +94,8 @@ CCFD_API int ccfd_forest_destroy(ccfd_forest* forest);
 /* The same validation and re-layout without a GPU: writes the packed image the kernels read
  * (all tree blobs back to back), 8 uint32 per tree {offset/16, bytes, leaf-value offset, depth,
  * first position whose leaf slot is not stored (= node count when all are), value index there,
- * 0, 0 (filled at create time)} and, if top_nodes is not NULL,
+ * 0 (filled at create time), node-encoding flag (bit 2 set: wide encoding, the forest has a tree
+ * beyond a shared-memory stage; clear: compact encoding)} and, if top_nodes is not NULL,
  * 14 uint32 per tree: the seven nodes of the top three levels as the STREAM kernel receives them.
  * Call with blob == NULL and tree_recs == NULL to learn *blob_bytes first.  Lets a deployment
  * build step (and the CPU tests) check a forest before it reaches a GPU; has no counterpart in
