@@ -280,10 +280,24 @@ def main():
             traffic = tj.get("dram_bytes_per_launch")
     except (OSError, ValueError):
         pass
+    # The resource that actually binds this kernel: shared-memory bank cycles.  Wavefront
+    # counts per launch come from the committed ncu capture, the time and the SM clock from this run.
+    on_chip = None
+    try:
+        sm_hz = float(clocks["sm_mhz"]) * 1e6
+        sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
+        if traffic is not None and sm_hz > 0:
+            lsu, tma = tj["smem_lsu_wavefronts_per_launch"], tj["smem_tma_write_lines_per_launch"]
+            cycles = kavg_ms * 1e-3 * sm_hz * sms
+            on_chip = {"resource": "shared-memory bank cycles (1 wavefront / clk / SM)", "lsu_read_frac": lsu / cycles,
+                       "tma_write_frac": tma / cycles, "frac": (lsu + tma) / cycles, "source": "profiles/traffic.json (ncu) x this run's time and clock",
+                       "note": "~1.0 = banks saturated; the TMA share is an upper bound (a write may use banks a read wavefront leaves idle)"}
+    except (KeyError, TypeError, ValueError, NameError):
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src, "kernel": "k_stream", "kernel_ms": kavg_ms,
                 "algorithmic_bytes_per_launch": algo_bytes,
-                "node_visits_per_s": n * fa.n_trees * info["max_depth"] / (kavg_ms * 1e-3)}
+                "node_visits_per_s": n * fa.n_trees * info["max_depth"] / (kavg_ms * 1e-3), "on_chip": on_chip}
 
     # ---- e2e: same rows from pinned host memory through the host-buffer call
     e2e = None
