@@ -153,6 +153,13 @@ int ccfd_cuda_fail(cudaError_t e, const char* what);
         if (_e != cudaSuccess) return ccfd_cuda_fail(_e, #call);     \
     } while (0)
 
+// Is `dev`'s primary context alive in this process?  (true when the driver cannot be asked)
+bool ccfd_primary_ctx_active(int dev);
+
+// Makes the forest's device current for the calling thread and puts the previous one back on exit --
+// unless the previous device has no context in this process: a thread that never chose a device
+// reports device 0, and cudaSetDevice(0) would then CREATE a context there (~1 s and several hundred
+// MB on a GPU this process does not use, e.g. every rank but 0 of a one-process-per-GPU job).
 class DeviceGuard {
   public:
     explicit DeviceGuard(int dev) {
@@ -161,7 +168,7 @@ class DeviceGuard {
         dev_ = dev;
     }
     ~DeviceGuard() {
-        if (prev_ >= 0 && prev_ != dev_) cudaSetDevice(prev_);
+        if (prev_ >= 0 && prev_ != dev_ && ccfd_primary_ctx_active(prev_)) cudaSetDevice(prev_);
     }
 
   private:

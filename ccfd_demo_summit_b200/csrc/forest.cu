@@ -25,6 +25,23 @@ int ccfd_fail(int code, const char* fmt, ...) {
     return code;
 }
 
+bool ccfd_primary_ctx_active(int dev) {
+    // cuDevicePrimaryCtxGetState through the runtime's driver entry-point lookup: no link-time dependency on
+    // libcuda, so the library still loads (for ccfd_forest_pack and the symbol checks) on a box without a driver.
+    using GetState = int (*)(int /*CUdevice*/, unsigned int* /*flags*/, int* /*active*/);
+    static const GetState fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult st;
+        if (cudaGetDriverEntryPoint("cuDevicePrimaryCtxGetState", &p, cudaEnableDefault, &st) != cudaSuccess || st != cudaDriverEntryPointSuccess) p = nullptr;
+        return reinterpret_cast<GetState>(p);
+    }();
+    if (!fn) return true;
+    unsigned int flags = 0;
+    int active = 0;
+    if (fn(dev, &flags, &active) != 0) return true;
+    return active != 0;
+}
+
 int ccfd_cuda_fail(cudaError_t e, const char* what) {
     snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
     cudaGetLastError();  // clear the non-sticky error state

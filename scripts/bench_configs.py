@@ -2,7 +2,8 @@
 
   config3  500-tree unbounded-depth forest on 10 M rows, one GPU, vs the memory roofline
   config5  mixed streaming load: concurrent single-transaction requests + back-to-back 65,536-row
-           batches on the same GPU (the 8-GPU case is 8 independent replicas of this)
+           batches on the same GPU; under `python -m torch.distributed.run --nproc-per-node N` every
+           GPU runs it at the same time and rank 0 prints the aggregate (configs[4] names 8 GPUs)
   easy     the 100-tree forest fitted on the Kaggle-like separable labels (tens of nodes per tree)
 
 Each prints one JSON line.  CPU comparators are scikit-learn on all host cores, bounded samples.
@@ -104,9 +105,19 @@ def easy(args):
 
 
 def config5(args):
+    # Under torch.distributed.run (one process per GPU) every rank runs the same mixed load on its own
+    # GPU at the same time; rank 0 prints the aggregate.  gloo is only used to line the phases up and
+    # to collect the per-GPU results: nothing is exchanged on the data path.
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("gloo")
+    sync = (lambda: dist.barrier()) if dist else (lambda: None)
     X, y = synth.make_dataset(seed=1, labels="hard")
     rf = synth.fit_forest(X, y)
-    forest = model.Forest(converter.from_sklearn(rf))
+    forest = model.Forest(converter.from_sklearn(rf), device=local)
     K = args.clients
     sess = model.Session(forest, 64, K)
     nb = 65536
@@ -116,6 +127,7 @@ def config5(args):
     batches = [0]
 
     def bulk():
+        torch.cuda.set_device(local)  # the current device is per thread
         st = torch.cuda.Stream()
         with torch.cuda.stream(st):
             while not stop.is_set():
@@ -143,23 +155,43 @@ def config5(args):
         lat = np.sort(np.concatenate([np.array(l[n_req // 10:]) for l in lats])) * 1e6
         return {"p50_us": float(lat[len(lat) // 2]), "p99_us": float(lat[int(len(lat) * .99)]), "req_s": K * n_req / dt}
 
+    sync()
     alone = run_clients(args.requests)
+    sync()
     ms_alone = time_device(forest, xs, nb, out)
+    sync()
     bt = threading.Thread(target=bulk)
     bt.start()
     time.sleep(0.2)
+    sync()
     b0, t0 = batches[0], time.perf_counter()
     mixed = run_clients(args.requests)
     dt = time.perf_counter() - t0
     b1 = batches[0]
+    sync()  # every GPU keeps its bulk stream busy until the slowest rank's clients are done
     stop.set()
     bt.join()
-    print(json.dumps({"config": "configs[4] on one GPU: single-transaction requests + back-to-back 65,536-row batches",
-                      "clients": K, "requests_per_client": args.requests,
-                      "single_alone": alone, "single_under_bulk": mixed,
-                      "bulk_alone_tx_s": nb / ms_alone * 1e3, "bulk_under_requests_tx_s": (b1 - b0) * nb / dt,
-                      "note": "requests run on highest-priority streams through per-client session slots (CUDA graphs); "
-                              "bulk batches on a default-priority stream, host-synchronous per batch"}), flush=True)
+    mine = {"single_alone": alone, "single_under_bulk": mixed, "bulk_alone_tx_s": nb / ms_alone * 1e3,
+            "bulk_under_requests_tx_s": (b1 - b0) * nb / dt}
+    note = ("requests run on highest-priority streams through per-client session slots (CUDA graphs); "
+            "bulk batches on a default-priority stream, host-synchronous per batch")
+    if world == 1:
+        print(json.dumps({"config": "configs[4] on one GPU: single-transaction requests + back-to-back 65,536-row batches",
+                          "clients": K, "requests_per_client": args.requests, **mine, "note": note}), flush=True)
+        return
+    every = [None] * world
+    dist.all_gather_object(every, mine)
+    if rank == 0:
+        agg = lambda k: {"p50_us_median_over_gpus": float(np.median([e[k]["p50_us"] for e in every])),  # noqa: E731
+                         "p99_us_max_over_gpus": float(max(e[k]["p99_us"] for e in every)),
+                         "req_s_total": float(sum(e[k]["req_s"] for e in every))}
+        print(json.dumps({"config": f"configs[4] on {world} GPUs: one replica, one process, {K} request clients and one bulk stream per GPU",
+                          "n_gpus": world, "clients_per_gpu": K, "requests_per_client": args.requests,
+                          "single_alone": agg("single_alone"), "single_under_bulk": agg("single_under_bulk"),
+                          "bulk_alone_tx_s_total": float(sum(e["bulk_alone_tx_s"] for e in every)),
+                          "bulk_under_requests_tx_s_total": float(sum(e["bulk_under_requests_tx_s"] for e in every)),
+                          "per_gpu": every, "note": note}), flush=True)
+    dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -404,3 +404,37 @@ def test_large_batch_properties(full_forest):
     dec = torch.empty(n, dtype=torch.uint8, device="cuda")
     forest.decide_device(xs.data_ptr(), n, 30, dec.data_ptr(), 0, 0.5, False, st, "stream")
     assert torch.equal(dec.bool(), out_s[:, 1] > 0.5)
+
+
+@pytest.mark.gpu
+def test_scoring_on_gpu1_from_a_fresh_thread_creates_no_context_on_gpu0():
+    """A thread that never chose a device reports device 0; putting "the previous device" back after a
+    call must not create a primary context there (every rank but 0 of a one-process-per-GPU job would
+    pay ~1 s and several hundred MB on GPU 0).  Needs two GPUs; runs in its own process."""
+    import subprocess
+    import sys
+
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    code = r'''
+import ctypes, threading, sys, numpy as np
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+from conftest import load_golden
+from ccfd_demo_summit_b200 import converter, model
+raw, X, P, *_ = load_golden("small_hard")
+fa = converter.from_arrays(raw.tree_offsets, raw.left, raw.right, raw.feature, raw.threshold, raw.missing_go_to_left, raw.value, raw.n_features, raw.n_classes)
+forest = model.Forest(fa, device=1)
+got = []
+t = threading.Thread(target=lambda: got.append(forest.predict_proba(X[:500])))
+t.start(); t.join()
+assert np.array_equal(np.ascontiguousarray(got[0]).view(np.uint64), np.ascontiguousarray(P[:500]).view(np.uint64))
+cu = ctypes.CDLL("libcuda.so.1")
+flags, active = ctypes.c_uint(), ctypes.c_int()
+assert cu.cuInit(0) == 0 and cu.cuDevicePrimaryCtxGetState(0, ctypes.byref(flags), ctypes.byref(active)) == 0
+print("active0", active.value)
+''' % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "active0 0" in r.stdout, r.stdout
