@@ -5,9 +5,12 @@
 //
 // Mapping, common to the three kernels: one lane = one row, so a row's float64 sum runs over
 // trees 0..T-1 in order inside one thread exactly as scikit-learn's n_jobs=1 loop does, and
-// results are bit-identical.  Rows live in shared memory transposed ([feature][row], row stride a
-// multiple of 32) so that the data-dependent `x[feature]` fetch of 32 lanes always hits 32
-// different banks.
+// results are bit-identical.  Rows live in shared memory transposed so that the data-dependent
+// `x[feature]` fetch of 32 lanes always hits 32 different banks: [feature][row] with a row stride
+// that is a multiple of 32, or, for up to 31 features, 64-row blocks of 32 feature rows on 8 KB
+// boundaries, where the address is one and-or of the node's meta word (XStrided / XBlocked below).
+// Nodes of forests that fit shared memory use the compact encoding of ccfd_internal.h: a level of a
+// chain is six instructions (LDS.64 node, LOP3 x address, LDS x, FSETP, SEL base, LEA.HI next).
 //
 //   STREAM  throughput.  A persistent CTA per SM keeps 512*SPT rows resident; rows (as row-major
 //           chunks) and the forest (as tree groups) arrive through one shared-memory ring fed by
