@@ -83,8 +83,13 @@ static_assert(sizeof(TreeRec) == 32, "TreeRec must be 32 bytes");
 // The top three levels of a tree in a fixed "virtual complete" order (root; its two children; the
 // four grandchildren), copies of the packed nodes.  Where a node of the top is a leaf, its slot
 // repeats downwards (a leaf steps to itself).
+#ifndef CCFD_TOP_LEVELS
+#define CCFD_TOP_LEVELS 3
+#endif
+constexpr int kTopLevels = CCFD_TOP_LEVELS;
+constexpr int kTopNodes = (1 << kTopLevels) - 1;
 struct TopNodes {
-    PackedNode n[7];
+    PackedNode n[kTopNodes];
 };
 
 // Everything a consumer warp needs to know about a tree, passed to the STREAM kernel BY VALUE so
@@ -92,7 +97,7 @@ struct TopNodes {
 // loads costs a full 32-lane write-back in the same L1/shared-memory data pipe that bounds the
 // kernel, the constant bank costs nothing there.
 struct TreeParam {
-    TopNodes top;          // 56 B
+    TopNodes top;          // 56 B (three levels)
     uint32_t rel_off;      // blob offset inside its stage
     uint32_t values_off;   // leaf values inside the blob
     uint32_t depth_flags;  // depth | first_of_group << 16 | last_of_group << 17
@@ -100,8 +105,8 @@ struct TreeParam {
     uint32_t last_vidx;
     uint32_t pad;
 };
-static_assert(sizeof(TreeParam) == 80, "TreeParam must be 80 bytes");
-constexpr int kMaxParamTrees = 400;  // 400 * 80 B = 32,000 B of the 32,764 B kernel parameter space
+static_assert(sizeof(TreeParam) == 8 * kTopNodes + 24, "TreeParam layout");
+constexpr int kMaxParamTrees = 32000 / (int)sizeof(TreeParam);  // 400 * 80 B = 32,000 B of the 32,764 B kernel parameter space
 
 // Consecutive trees whose blobs fit one shared-memory stage together: one bulk copy per group.
 struct GroupRec {

@@ -208,7 +208,7 @@ int pack_tree(const ccfd_forest_desc* d, int t, bool big, PackedTree* out) {
     auto is_leaf = [&](const PackedNode& n) { return feature_of(n) == (uint32_t)F; };
     TopNodes& tp = out->top;
     tp.n[0] = out->nodes[0];
-    for (int parent = 0; parent < 3; ++parent) {
+    for (int parent = 0; parent < (kTopNodes - 1) / 2; ++parent) {
         const PackedNode& pn = tp.n[parent];
         const uint32_t c = big ? NodeFmt<true>::child(pn.meta) : NodeFmt<false>::child(pn.meta);
         tp.n[2 * parent + 1] = out->nodes[c];

@@ -71,7 +71,8 @@ def _step(fmt, thr_bits, meta, x):
 
 def predict_proba(blob, recs, n_features, X32, top=None):
     """top=None: every level from the node array.  top given: the first three levels from the
-    seven-node table, picked with selects, as the STREAM kernel does (descend<TOP=true>)."""
+    seven-node table in virtual complete order (children of i at 2i+1, 2i+2), as the STREAM kernel
+    does with lane-indexed constant-bank loads (descend<TOP=true>)."""
     n = X32.shape[0]
     fmt = fmt_of(recs)
     xs = np.concatenate([X32, np.zeros((n, 1), np.float32)], axis=1)  # dummy feature row = 0
