@@ -178,31 +178,47 @@ extern "C" int ccfd_cast_rows(const void* src, int32_t src_is_f64, int64_t n, in
     unsigned hw = std::thread::hardware_concurrency();
     int nt = (int)std::min<int64_t>(std::max(1u, std::min(hw, 16u)), std::max<int64_t>(1, n * n_cols / 65536));
     std::vector<int> inf_seen((size_t)nt, 0);
+    // spans of contiguous values; +-inf is "exponent all ones, mantissa zero" (NaN is allowed): an integer
+    // test on the bits, which the host compiler vectorises
+    auto is_inf = [](float v) {
+        uint32_t u;
+        memcpy(&u, &v, 4);
+        return (int)((u & 0x7FFFFFFFu) == 0x7F800000u);
+    };
+    auto scan_f32 = [&](const float* sp, int64_t m) {
+        int bad = 0;
+        for (int64_t i = 0; i < m; ++i) bad |= is_inf(sp[i]);
+        return bad;
+    };
+    auto copy_f32 = [&](const float* sp, float* d, int64_t m) {
+        int bad = 0;
+        for (int64_t i = 0; i < m; ++i) {
+            d[i] = sp[i];
+            bad |= is_inf(sp[i]);
+        }
+        return bad;
+    };
+    auto cast_f64 = [&](const double* sp, float* d, int64_t m) {
+        int bad = 0;
+        for (int64_t i = 0; i < m; ++i) {
+            const float v = (float)sp[i];
+            d[i] = v;
+            bad |= is_inf(v);
+        }
+        return bad;
+    };
+    auto span = [&](int64_t r, int64_t m) {  // m contiguous source values starting at row r
+        if (!dst) return scan_f32(static_cast<const float*>(src) + r * src_ld, m);
+        if (src_is_f64) return cast_f64(static_cast<const double*>(src) + r * src_ld, dst + r * n_cols, m);
+        return copy_f32(static_cast<const float*>(src) + r * src_ld, dst + r * n_cols, m);
+    };
     auto work = [&](int k) {
         const int64_t r0 = n * k / nt, r1 = n * (k + 1) / nt;
         int bad = 0;
-        for (int64_t r = r0; r < r1; ++r) {
-            if (!dst) {  // float32 rows that need no copy: finiteness scan only
-                const float* s = static_cast<const float*>(src) + r * src_ld;
-                for (int64_t c = 0; c < n_cols; ++c) bad |= (s[c] - s[c] != 0.0f) & (s[c] == s[c]);
-                continue;
-            }
-            float* d = dst + r * n_cols;
-            if (src_is_f64) {
-                const double* s = static_cast<const double*>(src) + r * src_ld;
-                for (int64_t c = 0; c < n_cols; ++c) {
-                    const float v = (float)s[c];
-                    d[c] = v;
-                    bad |= (v - v != 0.0f) & (v == v);  // inf - inf is NaN, NaN itself is allowed
-                }
-            } else {
-                const float* s = static_cast<const float*>(src) + r * src_ld;
-                for (int64_t c = 0; c < n_cols; ++c) {
-                    const float v = s[c];
-                    d[c] = v;
-                    bad |= (v - v != 0.0f) & (v == v);
-                }
-            }
+        if (src_ld == n_cols) {
+            bad = span(r0, (r1 - r0) * n_cols);  // dense rows: one span
+        } else {
+            for (int64_t r = r0; r < r1; ++r) bad |= span(r, n_cols);
         }
         inf_seen[(size_t)k] = bad;
     };
