@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(PKG, "libccfd_rf.so")
 
 OK, EINVAL, ECUDA, ENOMEM, EUNSUPPORTED, ESTATE = 0, -1, -2, -3, -4, -5
 DEVICE_PTRS, ASYNC = 0x1, 0x2
+NOALLOC_MAX_TREE_ROWS = 1 << 20  # CCFD_NOALLOC_MAX_TREE_ROWS in include/ccfd_rf.h
 KERNEL_AUTO, KERNEL_STREAM, KERNEL_SPLIT, KERNEL_GLOBAL = 0x000, 0x100, 0x200, 0x300
 KERNELS = {"auto": KERNEL_AUTO, "stream": KERNEL_STREAM, "split": KERNEL_SPLIT, "global": KERNEL_GLOBAL}
 
@@ -52,6 +53,13 @@ SYMBOLS = [
     ("ccfd_session_submit", c_int, [c_void_p, c_int32, c_int64]),
     ("ccfd_session_wait", c_int, [c_void_p, c_int32]),
     ("ccfd_session_run", c_int, [c_void_p, c_int32, c_int64]),
+    ("ccfd_batcher_create", c_int, [c_void_p, c_int64, POINTER(c_void_p)]),
+    ("ccfd_batcher_destroy", c_int, [c_void_p]),
+    ("ccfd_batcher_push", c_int, [c_void_p, c_void_p, c_int64, c_int64]),
+    ("ccfd_batcher_flush", c_int, [c_void_p]),
+    ("ccfd_batcher_poll", c_int, [c_void_p, c_int32, POINTER(c_int64), POINTER(c_int64), c_void_p, c_int64, POINTER(c_double)]),
+    ("ccfd_batcher_replay", c_int, [c_void_p, c_void_p, c_int64, c_int64, c_double, c_int32]),
+    ("ccfd_batcher_stats", c_int, [c_void_p, POINTER(c_int64), POINTER(c_int64)]),
     ("ccfd_cast_rows", c_int, [c_void_p, c_int32, c_int64, c_int64, c_int64, c_void_p, POINTER(c_int32)]),
     ("ccfd_format_proba", c_int, [c_void_p, c_int64, c_void_p, c_int64, POINTER(c_int64)]),
     ("ccfd_parse_rows", c_int, [c_char_p, c_int64, c_int32, c_int32, c_void_p, c_int64, POINTER(c_int64)]),

@@ -101,12 +101,12 @@ int score_impl(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* ou
 
 }  // namespace
 
-extern "C" int ccfd_predict_proba(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint32_t flags, void* stream) {
+static int ccfd_predict_proba_impl(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint32_t flags, void* stream) {
     if (!out && n > 0) return ccfd_fail(CCFD_EINVAL, "out is null");
     return score_impl(f, X, n, ld, out, nullptr, 0.5, 0, flags, stream);
 }
 
-extern "C" int ccfd_predict_decision(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint8_t* decision, double threshold,
+static int ccfd_predict_decision_impl(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint8_t* decision, double threshold,
                                      int ge, uint32_t flags, void* stream) {
     if (!decision && n > 0) return ccfd_fail(CCFD_EINVAL, "decision is null");
     return score_impl(f, X, n, ld, out, decision, threshold, ge, flags, stream);
@@ -206,7 +206,7 @@ int build_slot(ccfd_session* ss, ccfd_slot& s) {
 
 }  // namespace
 
-extern "C" int ccfd_session_create(ccfd_forest* f, int64_t max_batch, int32_t n_slots, ccfd_session** out) {
+static int ccfd_session_create_impl(ccfd_forest* f, int64_t max_batch, int32_t n_slots, ccfd_session** out) {
     if (!f || !out) return ccfd_fail(CCFD_EINVAL, "null argument");
     *out = nullptr;
     if (max_batch < 1 || max_batch > (1 << 22)) return ccfd_fail(CCFD_EINVAL, "max_batch must be in 1..4194304 (got %lld)", (long long)max_batch);
@@ -230,7 +230,7 @@ extern "C" int ccfd_session_create(ccfd_forest* f, int64_t max_batch, int32_t n_
     return CCFD_OK;
 }
 
-extern "C" int ccfd_session_destroy(ccfd_session* ss) {
+static int ccfd_session_destroy_impl(ccfd_session* ss) {
     if (!ss) return CCFD_OK;
     DeviceGuard guard(ss->f->device);
     for (auto& s : ss->slots) free_slot(s);
@@ -238,7 +238,7 @@ extern "C" int ccfd_session_destroy(ccfd_session* ss) {
     return CCFD_OK;
 }
 
-extern "C" int ccfd_session_buffers(ccfd_session* ss, int32_t slot, float** x, double** p) {
+static int ccfd_session_buffers_impl(ccfd_session* ss, int32_t slot, float** x, double** p) {
     if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
     if (slot < 0 || slot >= (int32_t)ss->slots.size()) return ccfd_fail(CCFD_EINVAL, "slot %d out of range", slot);
     if (x) *x = ss->slots[(size_t)slot].hx;
@@ -246,7 +246,7 @@ extern "C" int ccfd_session_buffers(ccfd_session* ss, int32_t slot, float** x, d
     return CCFD_OK;
 }
 
-extern "C" int ccfd_session_submit(ccfd_session* ss, int32_t slot, int64_t n_rows) {
+static int ccfd_session_submit_impl(ccfd_session* ss, int32_t slot, int64_t n_rows) {
     if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
     if (slot < 0 || slot >= (int32_t)ss->slots.size()) return ccfd_fail(CCFD_EINVAL, "slot %d out of range", slot);
     if (n_rows < 1 || n_rows > ss->max_batch) return ccfd_fail(CCFD_EINVAL, "n_rows must be in 1..%lld (got %lld)", (long long)ss->max_batch, (long long)n_rows);
@@ -260,7 +260,7 @@ extern "C" int ccfd_session_submit(ccfd_session* ss, int32_t slot, int64_t n_row
     return CCFD_OK;
 }
 
-extern "C" int ccfd_session_wait(ccfd_session* ss, int32_t slot) {
+static int ccfd_session_wait_impl(ccfd_session* ss, int32_t slot) {
     if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
     if (slot < 0 || slot >= (int32_t)ss->slots.size()) return ccfd_fail(CCFD_EINVAL, "slot %d out of range", slot);
     ccfd_slot& s = ss->slots[(size_t)slot];
@@ -270,8 +270,42 @@ extern "C" int ccfd_session_wait(ccfd_session* ss, int32_t slot) {
     return CCFD_OK;
 }
 
-extern "C" int ccfd_session_run(ccfd_session* ss, int32_t slot, int64_t n_rows) {
+int ccfd_session_geometry(const ccfd_session* ss, int64_t* max_batch, int32_t* n_slots, int32_t* n_features) {
+    if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
+    if (max_batch) *max_batch = ss->max_batch;
+    if (n_slots) *n_slots = (int32_t)ss->slots.size();
+    if (n_features) *n_features = ss->f->dev.n_features;
+    return CCFD_OK;
+}
+
+static int ccfd_session_run_impl(ccfd_session* ss, int32_t slot, int64_t n_rows) {
     int rc = ccfd_session_submit(ss, slot, n_rows);
     if (rc != CCFD_OK) return rc;
     return ccfd_session_wait(ss, slot);
+}
+
+// ---- the C ABI: every body above runs inside ccfd_guarded (no C++ exception crosses the boundary)
+extern "C" int ccfd_predict_proba(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint32_t flags, void* stream) {
+    return ccfd_guarded("ccfd_predict_proba", [&]() -> int { return ccfd_predict_proba_impl(f, X, n, ld, out, flags, stream); });
+}
+extern "C" int ccfd_predict_decision(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint8_t* decision, double threshold, int ge, uint32_t flags, void* stream) {
+    return ccfd_guarded("ccfd_predict_decision", [&]() -> int { return ccfd_predict_decision_impl(f, X, n, ld, out, decision, threshold, ge, flags, stream); });
+}
+extern "C" int ccfd_session_create(ccfd_forest* f, int64_t max_batch, int32_t n_slots, ccfd_session** out) {
+    return ccfd_guarded("ccfd_session_create", [&]() -> int { return ccfd_session_create_impl(f, max_batch, n_slots, out); });
+}
+extern "C" int ccfd_session_destroy(ccfd_session* ss) {
+    return ccfd_guarded("ccfd_session_destroy", [&]() -> int { return ccfd_session_destroy_impl(ss); });
+}
+extern "C" int ccfd_session_buffers(ccfd_session* ss, int32_t slot, float** x, double** p) {
+    return ccfd_guarded("ccfd_session_buffers", [&]() -> int { return ccfd_session_buffers_impl(ss, slot, x, p); });
+}
+extern "C" int ccfd_session_submit(ccfd_session* ss, int32_t slot, int64_t n_rows) {
+    return ccfd_guarded("ccfd_session_submit", [&]() -> int { return ccfd_session_submit_impl(ss, slot, n_rows); });
+}
+extern "C" int ccfd_session_wait(ccfd_session* ss, int32_t slot) {
+    return ccfd_guarded("ccfd_session_wait", [&]() -> int { return ccfd_session_wait_impl(ss, slot); });
+}
+extern "C" int ccfd_session_run(ccfd_session* ss, int32_t slot, int64_t n_rows) {
+    return ccfd_guarded("ccfd_session_run", [&]() -> int { return ccfd_session_run_impl(ss, slot, n_rows); });
 }

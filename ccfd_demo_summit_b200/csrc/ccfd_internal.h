@@ -4,8 +4,13 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <exception>
+#include <functional>
 #include <mutex>
+#include <new>
+#include <stdexcept>
 #include <string>
+#include <system_error>
 #include <vector>
 
 #include "ccfd_rf.h"
@@ -158,6 +163,35 @@ int ccfd_cuda_fail(cudaError_t e, const char* what);
         if (_e != cudaSuccess) return ccfd_cuda_fail(_e, #call);     \
     } while (0)
 
+// Every extern "C" body runs inside ccfd_guarded: the header promises "never throws", and a C++
+// exception that crossed the C boundary (ctypes, cgo, JNI) would end the host process -- the Seldon
+// model server -- instead of failing one request.  Allocation failures (std::bad_alloc from vector /
+// map growth, std::system_error from thread creation) come back as CCFD_ENOMEM, anything else as
+// CCFD_ECUDA with the exception's text in ccfd_last_error().
+template <class F>
+int ccfd_guarded(const char* where, F&& body) noexcept {
+    try {
+        return body();
+    } catch (const std::bad_alloc&) {
+        return ccfd_fail(CCFD_ENOMEM, "%s: out of host memory", where);
+    } catch (const std::length_error& e) {
+        return ccfd_fail(CCFD_ENOMEM, "%s: %s", where, e.what());
+    } catch (const std::system_error& e) {
+        return ccfd_fail(CCFD_ENOMEM, "%s: %s", where, e.what());
+    } catch (const std::exception& e) {
+        return ccfd_fail(CCFD_ECUDA, "%s: unexpected failure: %s", where, e.what());
+    } catch (...) {
+        return ccfd_fail(CCFD_ECUDA, "%s: unexpected failure", where);
+    }
+}
+
+// Host worker pool shared by the multi-threaded host passes (ccfd_cast_rows, ccfd_parse_rows): threads
+// are created once, on first use, not per call.  Runs fn(0..n_parts-1); the calling thread takes part
+// in the work.  If the pool is busy with another caller, or its threads could not be created, the
+// caller simply runs every part itself.
+void ccfd_parallel_for(int n_parts, const std::function<void(int)>& fn);
+int ccfd_host_threads();  // parts worth asking for (pool size + the caller), >= 1
+
 // Is `dev`'s primary context alive in this process?  (true when the driver cannot be asked)
 bool ccfd_primary_ctx_active(int dev);
 
@@ -179,6 +213,9 @@ class DeviceGuard {
   private:
     int prev_ = -1, dev_ = 0;
 };
+
+// api.cu
+int ccfd_session_geometry(const ccfd_session* ss, int64_t* max_batch, int32_t* n_slots, int32_t* n_features);
 
 // kernels.cu -------------------------------------------------------------------------------------
 struct ScoreArgs {

@@ -291,7 +291,7 @@ int pack_forest(const ccfd_forest_desc* d, PackedForest* pf) {
 
 }  // namespace
 
-extern "C" int ccfd_forest_pack(const ccfd_forest_desc* d, void* blob, int64_t blob_capacity, uint32_t* tree_recs, uint32_t* top_nodes,
+static int ccfd_forest_pack_impl(const ccfd_forest_desc* d, void* blob, int64_t blob_capacity, uint32_t* tree_recs, uint32_t* top_nodes,
                                 int64_t* blob_bytes) {
     if (!blob_bytes) return ccfd_fail(CCFD_EINVAL, "null argument");
     PackedForest pf;
@@ -307,7 +307,7 @@ extern "C" int ccfd_forest_pack(const ccfd_forest_desc* d, void* blob, int64_t b
     return CCFD_OK;
 }
 
-extern "C" int ccfd_forest_create(const ccfd_forest_desc* d, int device, ccfd_forest** out) {
+static int ccfd_forest_create_impl(const ccfd_forest_desc* d, int device, ccfd_forest** out) {
     if (!d || !out) return ccfd_fail(CCFD_EINVAL, "null argument");
     *out = nullptr;
     PackedForest pf;
@@ -366,7 +366,7 @@ extern "C" int ccfd_forest_create(const ccfd_forest_desc* d, int device, ccfd_fo
     return CCFD_OK;
 }
 
-extern "C" int ccfd_forest_destroy(ccfd_forest* f) {
+static int ccfd_forest_destroy_impl(ccfd_forest* f) {
     if (!f) return CCFD_OK;
     DeviceGuard guard(f->device);
     for (int i = 0; i < 2; ++i) {
@@ -383,8 +383,22 @@ extern "C" int ccfd_forest_destroy(ccfd_forest* f) {
     return CCFD_OK;
 }
 
-extern "C" int ccfd_forest_get_info(const ccfd_forest* f, ccfd_forest_info* info) {
+static int ccfd_forest_get_info_impl(const ccfd_forest* f, ccfd_forest_info* info) {
     if (!f || !info) return ccfd_fail(CCFD_EINVAL, "null argument");
     *info = f->info;
     return CCFD_OK;
+}
+
+// ---- the C ABI: every body above runs inside ccfd_guarded (no C++ exception crosses the boundary)
+extern "C" int ccfd_forest_pack(const ccfd_forest_desc* d, void* blob, int64_t blob_capacity, uint32_t* tree_recs, uint32_t* top_nodes, int64_t* blob_bytes) {
+    return ccfd_guarded("ccfd_forest_pack", [&]() -> int { return ccfd_forest_pack_impl(d, blob, blob_capacity, tree_recs, top_nodes, blob_bytes); });
+}
+extern "C" int ccfd_forest_create(const ccfd_forest_desc* d, int device, ccfd_forest** out) {
+    return ccfd_guarded("ccfd_forest_create", [&]() -> int { return ccfd_forest_create_impl(d, device, out); });
+}
+extern "C" int ccfd_forest_destroy(ccfd_forest* f) {
+    return ccfd_guarded("ccfd_forest_destroy", [&]() -> int { return ccfd_forest_destroy_impl(f); });
+}
+extern "C" int ccfd_forest_get_info(const ccfd_forest* f, ccfd_forest_info* info) {
+    return ccfd_guarded("ccfd_forest_get_info", [&]() -> int { return ccfd_forest_get_info_impl(f, info); });
 }

@@ -53,7 +53,7 @@ int scratch_address(int device, void** out) {
 
 }  // namespace
 
-extern "C" int ccfd_predict_proba_noalloc(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, void* stream_) {
+static int ccfd_predict_proba_noalloc_impl(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, void* stream_) {
     if (!f) return ccfd_fail(CCFD_EINVAL, "null forest");
     if (n < 0) return ccfd_fail(CCFD_EINVAL, "n must be >= 0 (got %lld)", (long long)n);
     if (n == 0) return CCFD_OK;
@@ -75,4 +75,9 @@ extern "C" int ccfd_predict_proba_noalloc(ccfd_forest* f, const float* X, int64_
     if (rc != CCFD_OK) return rc;
     CCFD_CUDA(cudaStreamSynchronize(stream));
     return CCFD_OK;
+}
+
+// ---- the C ABI: every body above runs inside ccfd_guarded (no C++ exception crosses the boundary)
+extern "C" int ccfd_predict_proba_noalloc(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, void* stream_) {
+    return ccfd_guarded("ccfd_predict_proba_noalloc", [&]() -> int { return ccfd_predict_proba_noalloc_impl(f, X, n, ld, out, stream_); });
 }

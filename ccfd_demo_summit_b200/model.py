@@ -12,11 +12,13 @@ from __future__ import annotations
 import ctypes
 import os
 import pickle
+import queue
 import threading
+import time
 
 import numpy as np
 
-from . import _lib
+from . import _lib, metrics
 from .converter import ForestArrays, from_sklearn
 from .synth import FEATURE_NAMES
 
@@ -181,12 +183,18 @@ class MultiGpuForest:
     between GPUs: rows are independent.  ctypes releases the GIL, so the per-GPU
     calls overlap."""
 
-    def __init__(self, arrays: ForestArrays, devices=None):
+    def __init__(self, arrays: ForestArrays, devices=None, reuse=None):
+        """``reuse``: forests that already exist ({device: Forest}); they are used as the replica of their
+        device instead of uploading a second copy there, and are not closed by ``close()``."""
         n = _lib.check(_lib.lib().ccfd_device_count())
         self.devices = list(range(n)) if devices is None else [int(d) for d in devices]
         if not self.devices:
             raise RuntimeError("no CUDA device")
-        self.forests = [Forest(arrays, d) for d in self.devices]
+        if len(set(self.devices)) != len(self.devices):
+            raise ValueError(f"device listed twice: {self.devices}")
+        reuse = reuse or {}
+        self._owned = [d not in reuse for d in self.devices]
+        self.forests = [reuse[d] if d in reuse else Forest(arrays, d) for d in self.devices]
         self.n_features, self.n_trees = arrays.n_features, arrays.n_trees
 
     def predict_proba(self, X32: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
@@ -216,8 +224,9 @@ class MultiGpuForest:
         return out
 
     def close(self):
-        for f in self.forests:
-            f.close()
+        for f, mine in zip(self.forests, self._owned):
+            if mine:
+                f.close()
 
 
 def load_model_file(path: str) -> ForestArrays:
@@ -241,13 +250,15 @@ class CcfdForestModel:
     deploy/router.yaml:54-70): ``CCFD_MODEL_PATH`` (forest file), ``CCFD_DEVICE``
     (GPU index), ``CCFD_DEVICES`` (comma-separated GPU indices: bulk requests are row-sharded over
     them, one replica each), ``CCFD_SESSION_MAX_BATCH`` (requests up to this many rows take the
-    CUDA-graph path; 0 disables it), ``FRAUD_THRESHOLD`` (same name and default as the
+    CUDA-graph path; 0 disables it), ``CCFD_SESSION_SLOTS`` (how many such requests may be in flight at
+    once, default 4), ``FRAUD_THRESHOLD`` (same name and default as the
     router's).  A fitted forest or a ForestArrays can also be passed directly.
     """
 
     class_names = ["proba_0", "proba_1"]
 
-    def __init__(self, model=None, device: int | None = None, session_max_batch: int | None = None):
+    def __init__(self, model=None, device: int | None = None, session_max_batch: int | None = None,
+                 session_slots: int | None = None):
         if model is None:
             path = os.environ.get("CCFD_MODEL_PATH")
             if not path:
@@ -257,35 +268,68 @@ class CcfdForestModel:
         device = int(os.environ.get("CCFD_DEVICE", "0")) if device is None else device
         self.forest = Forest(arrays, device)
         devs = [int(d) for d in os.environ.get("CCFD_DEVICES", "").split(",") if d.strip() != ""]
-        self._multi = MultiGpuForest(arrays, devs) if len(devs) > 1 else None
+        # the forest above doubles as the replica of its own device: no second upload there
+        self._multi = MultiGpuForest(arrays, devs, reuse={self.forest.device: self.forest}) if len(devs) > 1 else None
         self.n_features_in_ = arrays.n_features
         self.classes_ = np.arange(arrays.n_classes)
         self.threshold = float(os.environ.get("FRAUD_THRESHOLD", "0.5"))
         smb = int(os.environ.get("CCFD_SESSION_MAX_BATCH", "1024")) if session_max_batch is None else session_max_batch
-        self._session = Session(self.forest, smb, n_slots=2) if smb > 0 else None
-        self._lock = threading.Lock()
+        n_slots = max(1, int(os.environ.get("CCFD_SESSION_SLOTS", "4")) if session_slots is None else int(session_slots))
+        self._session = Session(self.forest, smb, n_slots=n_slots) if smb > 0 else None
+        # Requests take a free slot and give it back: up to n_slots requests are in flight at once (copy-in,
+        # graph and wait of different slots overlap on their own streams); nothing else is shared between
+        # them, so no lock is held while a request is on the GPU.
+        self._free_slots = queue.SimpleQueue()
+        for k in range(n_slots if self._session is not None else 0):
+            self._free_slots.put(k)
         self._tls = threading.local()  # per-thread cast buffer (Seldon may run threaded workers)
-        self._slot = 0
-        self._last = None
+        self._last = None              # (row, probabilities) of the latest request: one tuple, swapped atomically
+        self._in_flight = 0
+        self.max_in_flight = 0         # high-water mark of concurrent session requests (observability, tests)
+        self._stat_lock = threading.Lock()
+        self.metrics_registry = reg = metrics.Registry()
+        reg.declare("ccfd_requests_total", "counter")
+        reg.declare("ccfd_rows_total", "counter")
+        reg.declare("ccfd_request_rows", "histogram", metrics.BATCH_BUCKETS)
+        reg.declare("ccfd_score_seconds", "histogram", metrics.LATENCY_BUCKETS)
+        reg.declare("ccfd_predict_seconds", "histogram", metrics.LATENCY_BUCKETS)
 
     def predict(self, X, feature_names=None, meta=None):
         """The Seldon wrapper passes the names positionally; like scikit-learn on a forest fitted
         from an ndarray, they are not used to reorder columns."""
+        t0 = time.perf_counter()
         tl = self._tls
         if not hasattr(tl, "scratch"):
             tl.scratch = {}
         X32 = validate_X(X, self.n_features_in_, tl.scratch)
         n = X32.shape[0]
+        t1 = time.perf_counter()
         if self._session is not None and n <= self._session.max_batch:
-            with self._lock:
-                slot = self._slot
-                self._slot = (slot + 1) % self._session.n_slots
+            slot = self._free_slots.get()  # blocks only when every slot is in flight
+            with self._stat_lock:
+                self._in_flight += 1
+                self.max_in_flight = max(self.max_in_flight, self._in_flight)
+            try:
                 P = self._session.score(slot, X32)
+            finally:
+                with self._stat_lock:
+                    self._in_flight -= 1
+                self._free_slots.put(slot)
+            path = "session"
         elif self._multi is not None and n >= 65536:
             P = self._multi.predict_proba(X32)
+            path = "multi_gpu"
         else:
             P = self.forest.predict_proba(X32)
-        self._last = (X32[-1].copy(), P[-1].copy())
+            path = "bulk"
+        t2 = time.perf_counter()
+        self._last = (X32[-1].copy(), P[-1].copy())  # the pair is built first, then published in one store
+        reg = self.metrics_registry
+        reg.inc("ccfd_requests_total", 1, path=path)
+        reg.inc("ccfd_rows_total", n, path=path)
+        reg.observe("ccfd_request_rows", n)
+        reg.observe("ccfd_score_seconds", t2 - t1, path=path)   # copy-in + kernels + result visible on the host
+        reg.observe("ccfd_predict_seconds", t2 - t0, path=path)  # with validation / cast
         return P
 
     def decide(self, X, threshold: float | None = None, ge: bool = False):

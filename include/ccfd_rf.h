@@ -168,22 +168,56 @@ CCFD_API int ccfd_session_wait(ccfd_session* session, int32_t slot);
  * per request instead of two). */
 CCFD_API int ccfd_session_run(ccfd_session* session, int32_t slot, int64_t n_rows);
 
+/* Micro-batcher over a session (BASELINE configs[1]: "1,024-transaction micro-batches replayed from a
+ * Kafka-shaped producer stream").  Replaces the per-message model call of the demo's router for the
+ * transactions the producer puts on topic odh-demo (reference deploy/kafka/ProducerDeployment.yaml:88-97,
+ * README.md:547-548).  Records are n_features float32 each (120 bytes for the demo's model).  The
+ * session's pinned slots are the ring: push copies records into the slot being filled, a slot that
+ * reaches batch_rows is submitted (one CUDA-graph launch) and the next one fills while it is in flight
+ * (the session needs >= 2 slots); a collector thread waits for submitted slots in order.  A batch's
+ * latency runs from the arrival of its last record to its results being visible in host memory.
+ * One producer thread (push / flush / replay) and one consumer thread (poll) at a time; push blocks
+ * while every slot is filling, in flight or not yet polled. */
+typedef struct ccfd_batcher ccfd_batcher;
+CCFD_API int ccfd_batcher_create(ccfd_session* session, int64_t batch_rows, ccfd_batcher** out);
+CCFD_API int ccfd_batcher_destroy(ccfd_batcher* batcher); /* drains what is in flight */
+/* n records, record stride `ld` floats (ld >= n_features).  A record holding +-inf is refused with
+ * CCFD_EINVAL (scikit-learn refuses it before scoring, SK/ensemble/_forest.py:606-625); NaN is allowed. */
+CCFD_API int ccfd_batcher_push(ccfd_batcher* batcher, const float* records, int64_t n, int64_t ld);
+CCFD_API int ccfd_batcher_flush(ccfd_batcher* batcher); /* submit a partly filled slot (end of stream, idle timeout) */
+/* Next completed batch, in submission order: returns 1 and fills *first_row (index of its first record
+ * in the stream), *n_rows, proba (n_rows x 2 float64 copied out of the slot, may be NULL) and
+ * *latency_us; returns 0 if none completed within timeout_ms (0 = do not wait).  Polling frees the slot. */
+CCFD_API int ccfd_batcher_poll(ccfd_batcher* batcher, int32_t timeout_ms, int64_t* first_row, int64_t* n_rows, double* proba,
+                               int64_t cap_rows, double* latency_us);
+/* Replay tool (the demo's producer replays creditcard.csv from S3): pushes `n` records from memory at
+ * records_per_s (<= 0: as fast as the ring takes them), `burst` records at a time as a consumer poll
+ * would deliver them, busy-waiting on the steady clock for each burst's due time, then flushes. */
+CCFD_API int ccfd_batcher_replay(ccfd_batcher* batcher, const float* records, int64_t n, int64_t ld, double records_per_s,
+                                 int32_t burst);
+CCFD_API int ccfd_batcher_stats(ccfd_batcher* batcher, int64_t* batches_done, int64_t* records_in);
+
 /* Request text -> float32 rows, written straight into `dst` (typically a session slot's pinned x
  * buffer, so the bytes the GPU copies are produced in one pass).  Replaces the JSON decoding of the
  * Seldon Python wrapper in front of predict() for requests arriving at reference
  * deploy/router.yaml:65-68, and the CSV handling of the Kafka consumer side of reference
- * deploy/kafka/ProducerDeployment.yaml:88-97.  Accepts Seldon JSON ("ndarray" or "tensor"/"values"
- * payloads; numbers before the payload key, e.g. "shape", are ignored), JSON lines, and CSV rows
- * (header words skipped, quoted numbers accepted).  Every `cols_in` numbers form a row and the first
- * `cols_keep` are kept (31 -> 30 drops the CSV's Class column).  Values take the same
- * text -> float64 -> float32 roundings as json.loads + numpy.  NaN/null -> NaN, Infinity -> inf
- * (for the caller to reject, as sklearn does).  Pure host code: no GPU is touched. */
+ * deploy/kafka/ProducerDeployment.yaml:88-97.  Accepts Seldon JSON ("ndarray": a matrix whose inner
+ * arrays are the rows; "tensor": {"shape":[n, cols_in], "values":[flat]}; nothing after the payload is
+ * read), JSON lines (one array or object per line; object keys are not cells), bare nested arrays, and
+ * CSV rows (a line of words only is a header and is skipped; quoted numbers accepted).  The decoder is
+ * structure-aware: every row must hold exactly `cols_in` numbers, of which the first `cols_keep` are
+ * kept (31 -> 30 drops the CSV's Class column); a row of another width, a non-numeric or boolean cell,
+ * a 1-D ndarray, or a tensor whose shape disagrees with its values is CCFD_EINVAL -- the payloads the
+ * Seldon wrapper + scikit-learn answer with a ValueError.  Cells are whole tokens ("Info" is a word,
+ * not inf).  Values take the same text -> float64 -> float32 roundings as json.loads + numpy.
+ * NaN/null -> NaN, Infinity -> inf (for the caller to reject, as sklearn does).  Newline-delimited
+ * inputs above 256 KB are parsed on the library's host worker pool.  Pure host code: no GPU is touched. */
 CCFD_API int ccfd_parse_rows(const char* text, int64_t len, int32_t cols_in, int32_t cols_keep, float* dst,
                              int64_t cap_rows, int64_t* n_rows);
 
 /* A float64 (src_is_f64 != 0) or float32 matrix of n rows x n_cols, row stride src_ld elements, ->
  * dense float32 rows in dst, and *has_inf = 1 if any narrowed value is +-inf (NaN is allowed), in one
- * multi-threaded pass.  Replaces the cast and the finiteness scan of
+ * pass (the library's persistent host worker pool for inputs above ~1 M values, the calling thread below).  Replaces the cast and the finiteness scan of
  * ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625); the narrowing is
  * bit-identical to numpy's astype(float32).  dst == NULL with float32 input scans only (rows that are
  * already dense float32 need no copy).  Pure host code. */

@@ -121,5 +121,49 @@ def main():
         json.dump(hashes, fh, indent=1)
 
 
+G3_TREES, G3_ROWS, G3_SEED = 500, 1_000_000, 33
+
+
+def g3_forest_and_rows():
+    """SURVEY.md §8c G3 = BASELINE configs[2]'s forest: 500 trees of unbounded depth fitted on the
+    284,807 hard-label rows, and a 1 M-row sample to score.  Shared with the GPU test, which refits
+    the forest on the box (the fit is reproducible: one seed per tree) and compares digests."""
+    X, y = synth.make_dataset(seed=1, labels="hard")
+    rf = synth.fit_forest(X, y, n_estimators=G3_TREES, max_depth=None, random_state=0)
+    return rf, synth.make_features(G3_ROWS, seed=G3_SEED)
+
+
+def main_g3():
+    """Too big to commit (107 MB packed, 16 MB of outputs): digests, the first 4,096 probability pairs
+    and the per-tree node statistics go into g_full_hashes.json / g3_head.npy."""
+    import time
+
+    t0 = time.time()
+    rf, Xq = g3_forest_and_rows()
+    t1 = time.time()
+    rf.n_jobs = 1  # tree order 0..T-1: the only bit-reproducible order
+    P = rf.predict_proba(Xq)
+    nodes = [int(e.tree_.node_count) for e in rf.estimators_]
+    depth = [int(e.tree_.max_depth) for e in rf.estimators_]
+    with open(os.path.join(HERE, "g_full_hashes.json")) as fh:
+        hashes = json.load(fh)
+    hashes["G3_unbounded"] = {
+        "trees": G3_TREES, "rows": G3_ROWS, "rows_seed": G3_SEED,
+        "X_sha256": hashlib.sha256(Xq.tobytes()).hexdigest(),
+        "P_sha256": hashlib.sha256(np.ascontiguousarray(P).tobytes()).hexdigest(),
+        "P_sha256_per_100k": [hashlib.sha256(np.ascontiguousarray(P[i:i + 100_000]).tobytes()).hexdigest()
+                              for i in range(0, G3_ROWS, 100_000)],
+        "nodes_min_mean_max": [min(nodes), float(np.mean(nodes)), max(nodes)], "n_nodes": int(sum(nodes)),
+        "depth_min_max": [min(depth), max(depth)],
+        "fraud_gt_0.5": int((P[:, 1] > 0.5).sum()), "fraud_ge_0.5": int((P[:, 1] >= 0.5).sum()),
+        "sklearn": sklearn.__version__, "numpy": np.__version__,
+    }
+    np.save(os.path.join(HERE, "g3_head.npy"), P[:4096])
+    with open(os.path.join(HERE, "g_full_hashes.json"), "w") as fh:
+        json.dump(hashes, fh, indent=1)
+    print(f"G3: fit {t1 - t0:.0f}s, predict {time.time() - t1:.0f}s, nodes {sum(nodes)}, depth {min(depth)}-{max(depth)}, "
+          f"P {hashes['G3_unbounded']['P_sha256'][:16]}")
+
+
 if __name__ == "__main__":
-    main()
+    main_g3() if "--g3" in sys.argv else main()

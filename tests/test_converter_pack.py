@@ -1,5 +1,6 @@
 """Converter + library re-layout, checked on the CPU against scikit-learn's outputs."""
 import ctypes
+import os
 
 import numpy as np
 import pytest
@@ -143,3 +144,39 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert getattr(L, name) is not None
     assert isinstance(L.ccfd_last_error(), bytes)
+
+
+def test_host_allocation_failure_comes_back_as_an_error_code():
+    """include/ccfd_rf.h promises "never throws": a std::bad_alloc inside the packer must come back as
+    CCFD_ENOMEM through the C ABI instead of ending the process.  Provoked for real, in a child process:
+    a one-tree forest of 6 M nodes (the packer's working vectors need several hundred MB) under an
+    address-space limit that leaves far less than that."""
+    import subprocess
+    import sys
+    import textwrap
+
+    code = textwrap.dedent(r'''
+        import ctypes, resource, sys
+        import numpy as np
+        sys.path.insert(0, %r)
+        from ccfd_demo_summit_b200 import _lib
+        L = _lib.lib()
+        n_int = 3_000_000                      # a comb: internal node i has the leaf 2i+1 and the internal node 2i+2
+        n = 2 * n_int + 1
+        left = np.full(n, -1, np.int32); right = np.full(n, -1, np.int32)
+        idx = np.arange(n_int, dtype=np.int64) * 2
+        left[idx] = (idx + 1).astype(np.int32); right[idx] = (idx + 2).astype(np.int32)
+        keep = [np.array([0, n], np.int64), np.zeros(n, np.int32), np.zeros(n, np.float32), left, right,
+                np.zeros(n, np.uint8), np.tile(np.array([0.5, 0.5]), (n, 1))]
+        d = _lib.ForestDesc(1, 30, 2, 0, *[a.ctypes.data_as(ctypes.c_void_p) for a in keep])
+        nbytes = ctypes.c_int64()
+        with open("/proc/self/statm") as fh:
+            vm_now = int(fh.read().split()[0]) * resource.getpagesize()
+        resource.setrlimit(resource.RLIMIT_AS, (vm_now + (48 << 20), vm_now + (48 << 20)))
+        rc = L.ccfd_forest_pack(ctypes.byref(d), None, 0, None, None, ctypes.byref(nbytes))
+        print("rc", rc, L.ccfd_last_error().decode())
+        sys.exit(0 if rc == _lib.ENOMEM else 3)
+    ''') % os.path.dirname(_lib.PKG)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.returncode, r.stdout[-500:], r.stderr[-1500:])
+    assert "out of host memory" in r.stdout

@@ -80,6 +80,100 @@ def test_parser_special_values_and_errors():
     assert sh.parse_rows_into(b"", dst) == 0
 
 
+def test_parser_is_structure_aware(rows):
+    """A row is what the payload says is a row.  Payloads the Seldon wrapper + scikit-learn answer with a
+    ValueError must not be re-cut every 30 numbers and scored (they used to be)."""
+    dst = np.zeros((64, 30), dtype=np.float32)
+    r64 = rows.astype(np.float64)
+    wide = np.concatenate([r64[:30], r64[:30, :1]], axis=1)                     # 30 rows x 31 columns = 31 x 30 numbers
+    ragged = [r64[0, :29].tolist() + [True], r64[1].tolist() + [1.0]]           # 29 numbers + true, then 31 numbers
+    bad = [
+        {"data": {"ndarray": wide.tolist()}},
+        {"data": {"ndarray": [np.concatenate([r64[0], r64[1]]).tolist()]}},     # one row of 60
+        {"data": {"ndarray": ragged}},
+        {"data": {"ndarray": r64[0].tolist()}},                                  # 1-D: not a matrix
+        {"data": {"ndarray": [r64[0].tolist(), r64[1, :29].tolist() + ["abc"]]}},
+        {"data": {"tensor": {"shape": [2, 31], "values": wide[:2].ravel().tolist()}}},
+        {"data": {"tensor": {"shape": [3, 30], "values": r64[:2].ravel().tolist()}}},
+        {"data": {"tensor": {"shape": [60], "values": r64[:2].ravel().tolist()}}},
+        {"data": {"tensor": {"values": r64[:2].ravel().tolist()}}},
+    ]
+    for payload in bad:
+        with pytest.raises(ValueError):
+            sh.parse_rows_into(json.dumps(payload).encode(), dst)
+    # what follows the payload is not read: numbers in "meta" are not cells
+    body = json.dumps({"data": {"names": ["a"], "ndarray": r64[:3].tolist()}, "meta": {"tags": {"k": [1, 2, 3]}, "puid": "7"}}).encode()
+    assert sh.parse_rows_into(body, dst) == 3 and np.array_equal(dst[:3].view(np.uint32), rows[:3].view(np.uint32))
+    body = json.dumps({"data": {"tensor": {"values": r64[:2].ravel().tolist(), "shape": [2, 30]}}, "meta": {"n": 5}}).encode()
+    assert sh.parse_rows_into(body, dst) == 2  # "values" before "shape"
+    # pretty-printed JSON: newlines inside an array do not end a row
+    body = json.dumps({"data": {"ndarray": r64[:2].tolist()}}, indent=2).encode()
+    assert sh.parse_rows_into(body, dst) == 2 and np.array_equal(dst[:2].view(np.uint32), rows[:2].view(np.uint32))
+    # CSV: header words are whole tokens ("Info", "Nanos" are not inf / nan), a header line is skipped,
+    # a line that mixes words and numbers or has the wrong width is refused
+    d3 = np.zeros((4, 3), dtype=np.float32)
+    assert sh.parse_rows_into(b"Info,Nanos,Time\n1,2,3\n\n4,nan,-inf\n", d3) == 2
+    assert d3[0].tolist() == [1.0, 2.0, 3.0] and d3[1, 0] == 4 and np.isnan(d3[1, 1]) and d3[1, 2] == -np.inf
+    for text in (b"1,2,x\n", b"1,2\n", b"1,2,3,4\n", b"1,2,3\n4,5\n", b"1,true,3\n", b"[[1,2,3],[4,[5,6]]]"):
+        with pytest.raises(ValueError):
+            sh.parse_rows_into(text, d3)
+    # JSON object per line: keys are not cells
+    assert sh.parse_rows_into(b'{"Time": 1, "V1": 2.5, "Amount": "3"}\n{"Time": 4, "V1": 5, "Amount": 6}', d3) == 2
+    assert d3[0].tolist() == [1.0, 2.5, 3.0]
+
+
+def test_large_record_blobs_are_parsed_on_the_host_pool_with_the_same_result(rows):
+    """A consumer poll of many messages (> 256 KB of text) is cut at line boundaries and parsed by the
+    persistent host pool; header and blank lines in the middle leave no holes."""
+    big = np.tile(rows, (80, 1))  # 5,120 records, ~1.4 MB of CSV
+    prod = ingest.KafkaShapedProducer(big, None)
+    lines = [prod.encode(i).decode() for i in range(len(big))]
+    lines.insert(0, ",".join(ingest.CSV_COLUMNS))
+    lines.insert(2500, "")
+    lines.insert(4000, ",".join(ingest.CSV_COLUMNS))
+    text = "\n".join(lines).encode()
+    assert len(text) > (1 << 20)
+    dst = np.full((len(big) + 3, 30), -1.0, dtype=np.float32)
+    assert sh.parse_rows_into(text, dst, 31) == len(big)
+    assert np.array_equal(dst[: len(big)].view(np.uint32), big.view(np.uint32))
+    with pytest.raises(ValueError):  # an error deep inside a chunk still surfaces
+        sh.parse_rows_into(text.replace(lines[3333].encode(), lines[3333].encode() + b",9"), dst, 31)
+    with pytest.raises(ValueError, match="more than"):
+        sh.parse_rows_into(text, dst[:100], 31)
+
+
+class _StubModel:
+    """Stands in for CcfdForestModel on a box without a GPU: same validation, constant output."""
+    n_features_in_ = 30
+
+    class _session:  # noqa: N801
+        max_batch = 64
+
+    def predict(self, X, names=None):
+        from ccfd_demo_summit_b200.model import validate_X
+
+        X32 = validate_X(X, 30)
+        return np.tile(np.array([[0.75, 0.25]]), (len(X32), 1))
+
+    def metrics(self):
+        return []
+
+    def tags(self):
+        return {}
+
+
+def test_seldon_app_refuses_misshapen_payloads_like_the_wrapper_would(rows):
+    app = sh.SeldonApp(_StubModel())
+    r64 = rows.astype(np.float64)
+    ok = json.loads(app.handle(json.dumps({"data": {"ndarray": r64[:3].tolist()}}).encode()))
+    assert len(ok["data"]["ndarray"]) == 3
+    wide = np.concatenate([r64[:30], r64[:30, :1]], axis=1)
+    for payload in ({"data": {"ndarray": wide.tolist()}}, {"data": {"ndarray": [np.concatenate([r64[0], r64[1]]).tolist()]}},
+                    {"data": {"ndarray": [r64[0, :29].tolist() + [True], r64[1].tolist() + [1.0]]}}):
+        with pytest.raises(ValueError):
+            app.handle(json.dumps(payload).encode())
+
+
 def test_encode_response_shape():
     P = np.array([[0.75, 0.25], [0.1, 0.9]])
     msg = json.loads(sh.encode_response(P, [{"type": "GAUGE", "key": "proba_1", "value": 0.9}], {"k": 1}))
