@@ -13,7 +13,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libccfd_rf.so")
-SOURCES = ["forest.cu", "kernels.cu", "api.cu", "no_alloc.cu", "ingest.cu", "batcher.cu"]
+SOURCES = ["forest.cu", "kernels.cu", "api.cu", "no_alloc.cu", "ingest.cu", "batcher.cu", "sort.cu"]
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-lineinfo",
     "-gencode", "arch=compute_100a,code=sm_100a",

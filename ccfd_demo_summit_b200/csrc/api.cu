@@ -37,8 +37,16 @@ int ensure_staging(ccfd_forest* f, int64_t rows) {
 int enqueue_device(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel, cudaStream_t stream) {
     if (kernel == CCFD_KERNEL_AUTO) kernel = ccfd_pick_kernel(f, a.n);
     void* scratch = nullptr;
-    if (kernel == CCFD_KERNEL_SPLIT) CCFD_CUDA(cudaMallocAsync(&scratch, (size_t)ccfd_split_scratch_bytes(f, a.n), stream));
-    int rc = ccfd_launch_score(f, a, kernel, scratch, stream);
+    ScoreArgs args = a;
+    int rc = CCFD_OK;
+    if (kernel == CCFD_KERNEL_SPLIT) {
+        CCFD_CUDA(cudaMallocAsync(&scratch, (size_t)ccfd_split_scratch_bytes(f, a.n), stream));
+    } else if (ccfd_row_sort_wanted(f, kernel, a.n)) {
+        // bulk GLOBAL launch: order the rows first so that a warp's rows share tree paths (sort.cu)
+        CCFD_CUDA(cudaMallocAsync(&scratch, (size_t)ccfd_sort_scratch_bytes(f, a.n), stream));
+        rc = ccfd_launch_row_sort(f, a.X, a.n, a.ld, scratch, &args.perm, stream);
+    }
+    if (rc == CCFD_OK) rc = ccfd_launch_score(f, args, kernel, scratch, stream);
     if (scratch) {
         cudaError_t e = cudaFreeAsync(scratch, stream);
         if (rc == CCFD_OK && e != cudaSuccess) return ccfd_cuda_fail(e, "cudaFreeAsync");
@@ -308,4 +316,14 @@ extern "C" int ccfd_session_wait(ccfd_session* ss, int32_t slot) {
 }
 extern "C" int ccfd_session_run(ccfd_session* ss, int32_t slot, int64_t n_rows) {
     return ccfd_guarded("ccfd_session_run", [&]() -> int { return ccfd_session_run_impl(ss, slot, n_rows); });
+}
+
+// Which kernel CCFD_KERNEL_AUTO resolves to for a batch of n rows (one of CCFD_KERNEL_STREAM / SPLIT / GLOBAL).
+extern "C" int ccfd_kernel_for(const ccfd_forest* f, int64_t n, uint32_t* kernel, int32_t* rows_presorted) {
+    return ccfd_guarded("ccfd_kernel_for", [&]() -> int {
+        if (!f || !kernel) return ccfd_fail(CCFD_EINVAL, "null argument");
+        *kernel = ccfd_pick_kernel(f, n);
+        if (rows_presorted) *rows_presorted = ccfd_row_sort_wanted(f, *kernel, n) ? 1 : 0;
+        return CCFD_OK;
+    });
 }

@@ -136,9 +136,18 @@ struct ForestDev {
     uint32_t wide_nodes;     // node encoding: 0 compact, 1 wide (see PackedNode)
 };
 
+// Row pre-sort key (sort.cu): up to 11 features x 2 bits, most used split feature in the top bits.
+constexpr int kSortMaxFeatures = 11;
+struct SortKey {
+    int32_t n_feat;
+    int32_t feat[kSortMaxFeatures];
+    float cut[kSortMaxFeatures][3];
+};
+
 struct ccfd_forest {
     int device = 0;
     ForestDev dev{};
+    SortKey sort_key{};
     ccfd_forest_info info{};
     std::vector<TreeRec> host_trees;
     std::vector<TopNodes> host_top;
@@ -226,6 +235,7 @@ struct ScoreArgs {
     uint8_t* decision;  // device, may be null
     double threshold;
     int ge;
+    const uint32_t* perm = nullptr;  // device, optional (GLOBAL kernel): row i of the launch is row perm[i] of X / out / decision
 };
 
 // Pick + launch.  `kernel` is one of CCFD_KERNEL_*; scratch is used by SPLIT only
@@ -235,3 +245,10 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
 uint32_t ccfd_pick_kernel(const ccfd_forest* f, int64_t n);
 int64_t ccfd_split_scratch_bytes(const ccfd_forest* f, int64_t n);
 int ccfd_kernels_init(ccfd_forest* f);
+
+// sort.cu ----------------------------------------------------------------------------------------
+void ccfd_sort_key_from_desc(const ccfd_forest_desc* d, SortKey* sk);
+int64_t ccfd_sort_scratch_bytes(const ccfd_forest* f, int64_t n);
+int ccfd_launch_row_sort(const ccfd_forest* f, const float* X, int64_t n, int64_t ld, void* scratch, const uint32_t** perm_out,
+                         cudaStream_t stream);
+bool ccfd_row_sort_wanted(const ccfd_forest* f, uint32_t kernel, int64_t n);

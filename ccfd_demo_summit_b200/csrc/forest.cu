@@ -323,6 +323,7 @@ static int ccfd_forest_create_impl(const ccfd_forest_desc* d, int device, ccfd_f
     f->device = device;
     f->host_trees = pf.trees;
     f->host_top = pf.top;
+    ccfd_sort_key_from_desc(d, &f->sort_key);
     const std::vector<uint8_t>& blob = pf.blob;
     const int64_t n_nodes = pf.n_nodes, n_leaves = pf.n_leaves;
     const uint32_t max_depth = pf.max_depth, max_bytes = pf.max_bytes;

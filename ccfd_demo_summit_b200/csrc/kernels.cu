@@ -639,7 +639,23 @@ __global__ void __launch_bounds__(kGlobalThreads) k_global(const ForestDev f, co
     const int64_t row0 = (int64_t)blockIdx.x * S;
     const int rows = (int)((a.n - row0) < (int64_t)S ? (a.n - row0) : (int64_t)S);
     for (int i = tid; i < XS; i += kGlobalThreads) xs[F * XS + i] = 0.0f;
-    const bool my_nan = load_tile<kGlobalThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+    bool my_nan;
+    if (a.perm) {
+        // pre-sorted launch (sort.cu): row r of this tile is row perm[row0 + r] of X.  A warp copies one row
+        // at a time (lanes = consecutive features: one or two sectors per row), zero-fills the ragged tail.
+        my_nan = false;
+        const int lane = tid & 31, warp = tid >> 5;
+        for (int r = warp; r < S; r += kGlobalThreads / 32) {
+            const float* src = r < rows ? a.X + (int64_t)__ldg(a.perm + row0 + r) * a.ld : nullptr;
+            for (int c = lane; c < F; c += 32) {
+                const float v = src ? __ldg(src + c) : 0.0f;
+                xs[c * XS + r] = v;
+                my_nan |= (v != v);
+            }
+        }
+    } else {
+        my_nan = load_tile<kGlobalThreads, S>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+    }
     const bool any_nan = __syncthreads_or(my_nan) != 0;
 
     double acc0 = 0.0, acc1 = 0.0;
@@ -674,8 +690,9 @@ __global__ void __launch_bounds__(kGlobalThreads) k_global(const ForestDev f, co
     if (tid < rows) {
         const double Td = (double)T;
         const double p0 = acc0 / Td, p1 = acc1 / Td;
-        if (a.out) reinterpret_cast<double2*>(a.out)[row0 + tid] = make_double2(p0, p1);
-        if (a.decision) a.decision[row0 + tid] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
+        const int64_t dst = a.perm ? (int64_t)__ldg(a.perm + row0 + tid) : row0 + tid;
+        if (a.out) reinterpret_cast<double2*>(a.out)[dst] = make_double2(p0, p1);
+        if (a.decision) a.decision[dst] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
     }
 }
 
@@ -882,6 +899,9 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));   \
     CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
         CCFD_GLOBAL_ATTRS(1, kGlobalThreadsBulk)
+        CCFD_GLOBAL_ATTRS(4, kGlobalThreadsBulk)
+        CCFD_GLOBAL_ATTRS(4, kGlobalThreadsSmall)
+        CCFD_GLOBAL_ATTRS(4, kGlobalThreadsWide)
         CCFD_GLOBAL_ATTRS(2, kGlobalThreadsBulk)
         CCFD_GLOBAL_ATTRS(1, kGlobalThreadsSmall)
         CCFD_GLOBAL_ATTRS(2, kGlobalThreadsSmall)
@@ -942,6 +962,18 @@ int ccfd_kernels_init(ccfd_forest* f) {
     return CCFD_OK;
 }
 
+// The row pre-sort pays where node loads go through L1/L2 (GLOBAL) and the launch is long enough to hide
+// it; CCFD_ROW_SORT=0 switches it off (A/B runs, tests), CCFD_ROW_SORT_MIN moves the threshold.
+bool ccfd_row_sort_wanted(const ccfd_forest* f, uint32_t kernel, int64_t n) {
+    if (kernel != CCFD_KERNEL_GLOBAL || f->sort_key.n_feat < 4) return false;
+    int64_t min_rows = 262144;
+    if (const char* e = getenv("CCFD_ROW_SORT")) {  // read per call: a knob for experiments, not a hot path
+        if (atoi(e) == 0) return false;
+    }
+    if (const char* e = getenv("CCFD_ROW_SORT_MIN")) min_rows = atoll(e);
+    return n >= min_rows && n <= 0xFFFFFFFFll;
+}
+
 uint32_t ccfd_pick_kernel(const ccfd_forest* f, int64_t n) {
     if (!f->info.stream_kernel_ok) return CCFD_KERNEL_GLOBAL;
     // Measured crossover on the 100-tree forest: SPLIT 44 / 64 / 86 us at 16k / 32k / 48k rows, STREAM a
@@ -958,6 +990,7 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
     if (reinterpret_cast<uintptr_t>(a.X) & 3u) return ccfd_fail(CCFD_EINVAL, "X must be 4-byte aligned");
     const int vec_ok = (a.ld == f->dev.n_features) && ((reinterpret_cast<uintptr_t>(a.X) & 15u) == 0);
     if (kernel == CCFD_KERNEL_AUTO) kernel = ccfd_pick_kernel(f, a.n);
+    if (a.perm && kernel != CCFD_KERNEL_GLOBAL) return ccfd_fail(CCFD_EINVAL, "internal: a row permutation is only understood by the GLOBAL kernel");
 
     if (kernel == CCFD_KERNEL_STREAM) {
         // two rows per thread (1,024 resident rows per CTA) as soon as 512-row batches would need
@@ -1051,7 +1084,8 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         const bool wide = f->dev.wide_nodes != 0;
 #define CCFD_LAUNCH_GLOBAL(TH_)                                                                        \
     do {                                                                                               \
-        if (nt == 2 && wide) k_global<2, TH_, true><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);        \
+        if (nt == 4 && wide) k_global<4, TH_, true><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);        \
+        else if (nt == 2 && wide) k_global<2, TH_, true><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);        \
         else if (nt == 2) k_global<2, TH_, false><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);          \
         else if (wide) k_global<1, TH_, true><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);              \
         else k_global<1, TH_, false><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);                       \

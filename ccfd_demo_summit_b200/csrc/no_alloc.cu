@@ -20,6 +20,11 @@
 //     keep calls on one GPU strictly one after another.
 //   * The first call on each GPU looks the array's device address up (cudaGetSymbolAddress) and
 //     keeps it.  Make that first call during start-up, before any CUDA stream capture begins.
+//     With CUDA's lazy module loading that look-up is also what loads this library's device image
+//     on the GPU, so "no allocation" holds from the second call on; the warm-up call is where the
+//     16 MiB come into existence.  The kept address belongs to the GPU's primary context: after a
+//     cudaDeviceReset() (or any other teardown of that context) it is stale and the process must
+//     not call this entry point again.
 #include <mutex>
 
 #include "ccfd_internal.h"

@@ -75,6 +75,18 @@ def validate_X(X, n_features: int, scratch=None) -> np.ndarray:
     return X32
 
 
+def packed_model_bytes(arrays: ForestArrays) -> int:
+    """Bytes of the packed device image of a forest (what one launch reads of the model), computed on the
+    host by ccfd_forest_pack: the same figure Forest.info["model_bytes"] reports, without a GPU."""
+    a = arrays
+    keep = [np.ascontiguousarray(x) for x in
+            (a.tree_offsets, a.feature, a.threshold, a.left, a.right, a.missing_go_to_left, a.value)]
+    d = _lib.ForestDesc(a.n_trees, a.n_features, a.n_classes, 0, *[_ptr(x) for x in keep])
+    nbytes = ctypes.c_int64()
+    _lib.check(_lib.lib().ccfd_forest_pack(ctypes.byref(d), None, 0, None, None, ctypes.byref(nbytes)))
+    return int(nbytes.value) + 32 * a.n_trees
+
+
 class Forest:
     """A forest resident on one GPU (opaque ``ccfd_forest`` handle)."""
 
@@ -106,6 +118,12 @@ class Forest:
             self._h = ctypes.c_void_p()
 
     __del__ = close
+
+    def kernel_for(self, n: int):
+        """(kernel name, rows pre-sorted?) that ``kernel="auto"`` means for a batch of n rows."""
+        k, srt = ctypes.c_uint32(), ctypes.c_int32()
+        _lib.check(_lib.lib().ccfd_kernel_for(self.handle, int(n), ctypes.byref(k), ctypes.byref(srt)))
+        return {v: name for name, v in _lib.KERNELS.items()}[k.value], bool(srt.value)
 
     # -- host buffers ---------------------------------------------------------------------
     def predict_proba(self, X32: np.ndarray, kernel: str = "auto", out: np.ndarray | None = None) -> np.ndarray:

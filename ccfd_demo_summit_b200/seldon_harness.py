@@ -16,13 +16,14 @@ from __future__ import annotations
 
 import ctypes
 import json
+import os
 import threading
 import time
 from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 
 import numpy as np
 
-from . import _lib
+from . import _lib, metrics
 
 PREDICT_PATHS = ("/api/v0.1/predictions", "/predict", "/api/v1.0/predictions")
 
@@ -77,12 +78,38 @@ def encode_response(P: np.ndarray, metrics=None, tags=None) -> bytes:
 
 
 class SeldonApp:
-    """Body in, body out: what the wrapper does between the HTTP layer and ``predict()``."""
+    """Body in, body out: what the wrapper does between the HTTP layer and ``predict()``.
 
-    def __init__(self, model, fast_decode: bool = True):
+    ``coalesce`` (or ``CCFD_COALESCE=1``): single-transaction requests (the jBPM/Camel pattern, reference
+    deploy/ccd-service.yaml:61-66) go through a RequestCoalescer, so requests that arrive while a launch
+    is in flight share the next one.  The app also keeps the request histograms the SeldonCore board
+    plots (reference deploy/grafana/SeldonCore.json:119-531) under the engine's metric names."""
+
+    LABELS = {"deployment_name": "modelfull", "predictor_name": "modelfull", "predictor_version": "v1",
+              "model_name": "modelfull", "model_image": "libccfd_rf", "model_version": "sm_100a"}
+
+    def __init__(self, model, fast_decode: bool = True, coalesce: bool | None = None):
         self.model = model
         self.fast_decode = fast_decode and getattr(model, "_session", None) is not None
         self._scratch = threading.local()
+        self.registry = reg = getattr(model, "metrics_registry", None) or metrics.Registry()
+        reg.declare("seldon_api_engine_server_requests_seconds", "histogram", metrics.LATENCY_BUCKETS)
+        reg.declare("seldon_api_engine_client_requests_seconds", "histogram", metrics.LATENCY_BUCKETS)
+        if coalesce is None:
+            coalesce = os.environ.get("CCFD_COALESCE", "0") not in ("", "0")
+        self.coalescer = None
+        if coalesce and self.fast_decode:
+            self.coalescer = RequestCoalescer(lambda M: model.predict(M, None), model.n_features_in_,
+                                              max_batch=model._session.max_batch, max_delay_s=0.0)
+
+    def _predict(self, X, names):
+        t = time.perf_counter()
+        try:
+            if self.coalescer is not None and len(X) == 1 and isinstance(X, np.ndarray) and X.dtype == np.float32:
+                return self.coalescer.score(X)
+            return self.model.predict(X, names)
+        finally:
+            self.registry.observe("seldon_api_engine_client_requests_seconds", time.perf_counter() - t, status="200", **self.LABELS)
 
     def handle(self, body: bytes) -> bytes:
         m = self.model
@@ -95,14 +122,31 @@ class SeldonApp:
             except ValueError:
                 n = -1  # oversize or irregular payload: let the reference decoder produce the error or the matrix
             if n > 0:
-                P = m.predict(buf[:n], None)
+                P = self._predict(buf[:n], None)
                 return encode_response(P, m.metrics(), m.tags())
         X, names = decode_request(body)
-        return encode_response(m.predict(X, names), m.metrics(), m.tags())
+        return encode_response(self._predict(X, names), m.metrics(), m.tags())
+
+    def serve(self, body: bytes):
+        """handle() with the status mapping of the HTTP layer: (status code, response body)."""
+        t = time.perf_counter()
+        try:
+            out, code = self.handle(body), 200
+        except ValueError as e:
+            out, code = json.dumps({"status": {"code": 400, "info": str(e), "status": "FAILURE"}}).encode(), 400
+        except Exception as e:  # noqa: BLE001  (CUDA failure etc.: 5xx, process stays up)
+            out, code = json.dumps({"status": {"code": 500, "info": str(e), "status": "FAILURE"}}).encode(), 500
+        self.registry.observe("seldon_api_engine_server_requests_seconds", time.perf_counter() - t, status=str(code), **self.LABELS)
+        return code, out
+
+    def close(self):
+        if self.coalescer is not None:
+            self.coalescer.close()
+            self.coalescer = None
 
 
-def make_server(model, host="127.0.0.1", port=8000) -> ThreadingHTTPServer:
-    app = SeldonApp(model)
+def make_server(model, host="127.0.0.1", port=8000, coalesce: bool | None = None) -> ThreadingHTTPServer:
+    app = SeldonApp(model, coalesce=coalesce)
 
     class Handler(BaseHTTPRequestHandler):
         def log_message(self, *a):  # quiet
@@ -113,12 +157,7 @@ def make_server(model, host="127.0.0.1", port=8000) -> ThreadingHTTPServer:
                 self.send_error(404)
                 return
             body = self.rfile.read(int(self.headers.get("Content-Length", "0")))
-            try:
-                out, code = app.handle(body), 200
-            except ValueError as e:
-                out, code = json.dumps({"status": {"code": 400, "info": str(e), "status": "FAILURE"}}).encode(), 400
-            except Exception as e:  # noqa: BLE001  (CUDA failure etc.: 5xx, process stays up)
-                out, code = json.dumps({"status": {"code": 500, "info": str(e), "status": "FAILURE"}}).encode(), 500
+            code, out = app.serve(body)
             self.send_response(code)
             self.send_header("Content-Type", "application/json")
             self.send_header("Content-Length", str(len(out)))
@@ -127,7 +166,7 @@ def make_server(model, host="127.0.0.1", port=8000) -> ThreadingHTTPServer:
 
         def do_GET(self):
             if self.path.startswith("/prometheus") or self.path.startswith("/metrics"):
-                out = prometheus_text(model).encode()
+                out = prometheus_text(model, app.registry).encode()
                 self.send_response(200)
                 self.send_header("Content-Type", "text/plain; version=0.0.4")
                 self.send_header("Content-Length", str(len(out)))
@@ -136,17 +175,25 @@ def make_server(model, host="127.0.0.1", port=8000) -> ThreadingHTTPServer:
             else:
                 self.send_error(404)
 
-    return ThreadingHTTPServer((host, port), Handler)
+    srv = ThreadingHTTPServer((host, port), Handler)
+    srv.app = app
+    return srv
 
 
-def prometheus_text(model) -> str:
+def prometheus_text(model, registry=None) -> str:
     """The model-level gauges of reference deploy/grafana/ModelPrediction.json:96,104,211,322 in
-    Prometheus exposition format (the model service is scraped at /prometheus, README.md:292-301)."""
+    Prometheus exposition format (the model service is scraped at /prometheus, README.md:292-301),
+    followed by the counters and histograms of the model (requests, rows, request sizes, scoring time)
+    and of the request layer (the SeldonCore board's seldon_api_engine_* families)."""
     lines = []
     for g in model.metrics():
         lines.append(f"# TYPE {g['key']} gauge")
         lines.append(f"{g['key']} {g['value']!r}")
-    return "\n".join(lines) + "\n"
+    text = "\n".join(lines) + "\n"
+    registry = registry or getattr(model, "metrics_registry", None)
+    if registry is not None:
+        text += registry.exposition()
+    return text
 
 
 class RequestCoalescer:
@@ -186,9 +233,16 @@ class RequestCoalescer:
                     self._cv.wait()
                 if self._stop and not self._pending:
                     return
-            if self.max_delay_s > 0:
-                time.sleep(self.max_delay_s)  # let concurrent callers join this batch
-            with self._cv:
+                if self.max_delay_s > 0:
+                    # wait for company until the first request's deadline or a full batch, whichever is first
+                    deadline = time.perf_counter() + self.max_delay_s
+                    while sum(r.shape[0] for r, _ in self._pending) < self.max_batch:
+                        left = deadline - time.perf_counter()
+                        if left <= 0 or self._stop:
+                            break
+                        self._cv.wait(left)
+                # max_delay_s == 0: no artificial wait.  Whatever queued while the previous launch was in
+                # flight forms this batch, so an idle server adds nothing to a lone request's latency.
                 take, total = [], 0
                 while self._pending and total + self._pending[0][0].shape[0] <= self.max_batch:
                     r, h = self._pending.pop(0)

@@ -121,6 +121,11 @@ CCFD_API int ccfd_forest_get_info(const ccfd_forest* forest, ccfd_forest_info* i
 CCFD_API int ccfd_predict_proba(ccfd_forest* forest, const float* X, int64_t n, int64_t ld, double* out,
                        uint32_t flags, void* stream);
 
+/* Which kernel CCFD_KERNEL_AUTO resolves to for a batch of n rows (*kernel = CCFD_KERNEL_STREAM, _SPLIT or
+ * _GLOBAL) and whether a device-pointer call of that size orders its rows first (*rows_presorted, may be
+ * NULL; see csrc/sort.cu).  For reports and tests; no counterpart in scikit-learn, which has one code path. */
+CCFD_API int ccfd_kernel_for(const ccfd_forest* forest, int64_t n, uint32_t* kernel, int32_t* rows_presorted);
+
 /* Same scoring, plus the router's rule fused into the epilogue: decision[i] = 1
  * iff p_fraud (op) threshold, op being `>` (ge == 0) or `>=` (ge != 0).
  * Replaces the Drools rule on the returned probability against
@@ -142,8 +147,10 @@ CCFD_API int ccfd_predict_decision(ccfd_forest* forest, const float* X, int64_t 
  *   sharing  one scratch per GPU, shared by all calls and left as the last call wrote it.  No
  *            clearing is needed (each call writes every slot it later reads), but calls that
  *            overlap on one GPU race on it: issue them one after another.
- *   set-up   the first call on each GPU resolves the array's device address and caches it; make
- *            that call at start-up, before any CUDA stream capture. */
+ *   set-up   the first call on each GPU resolves the array's device address and caches it (which,
+ *            with lazy module loading, is also when the GPU loads the library image and the 16 MiB
+ *            appear); make that call at start-up, before any CUDA stream capture.  The cached address
+ *            dies with the GPU's primary context: do not call again after cudaDeviceReset(). */
 #define CCFD_NOALLOC_MAX_TREE_ROWS (1 << 20)
 CCFD_API int ccfd_predict_proba_noalloc(ccfd_forest* forest, const float* X, int64_t n, int64_t ld, double* out,
                                         void* stream);

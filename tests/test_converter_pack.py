@@ -144,6 +144,9 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert getattr(L, name) is not None
     assert isinstance(L.ccfd_last_error(), bytes)
+    # constants mirrored in the binding
+    m = re.search(r"#define CCFD_NOALLOC_MAX_TREE_ROWS \(1 << (\d+)\)", header)
+    assert m and _lib.NOALLOC_MAX_TREE_ROWS == 1 << int(m.group(1))
 
 
 def test_host_allocation_failure_comes_back_as_an_error_code():

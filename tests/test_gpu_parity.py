@@ -143,6 +143,25 @@ def test_unbounded_depth_forest_goes_through_the_global_kernel(ccfd):
     m.close()
 
 
+def test_row_presort_changes_no_bit(ccfd, monkeypatch):
+    """Bulk GLOBAL launches take their rows in key order (csrc/sort.cu); rows are scored independently,
+    so results land on the original rows and no bit changes.  The threshold is lowered so that small,
+    ragged, strided and NaN-carrying batches go through the sort too."""
+    _, model = ccfd
+    monkeypatch.setenv("CCFD_ROW_SORT_MIN", "1")
+    for name in ("deep", "small_hard", "nan_trained", "bestfirst"):
+        raw, X, P, _ = load_golden(name)
+        forest = model.Forest(_fa(raw))
+        X32 = np.ascontiguousarray(X, dtype=np.float32)
+        for n in (1, 33, 257, len(X32)):
+            assert np.array_equal(bits(_score_device(forest, X32[:n], "global")), bits(P[:n])), (name, n)
+        assert np.array_equal(bits(_score_device(forest, X32, "global", ld=41)), bits(P)), name
+        assert np.array_equal(bits(_score_device(forest, X32, "global", misalign=True)), bits(P)), name
+        d, p = forest.decide(X32, 0.5, ge=True, want_proba=True, kernel="global")
+        assert np.array_equal(d, P[:, 1] >= 0.5) and np.array_equal(bits(p), bits(P)), name
+        forest.close()
+
+
 def test_fused_decision_matches_threshold_rule(ccfd):
     _, model = ccfd
     raw, X, P, _ = load_golden("deep")  # pure leaves: p is k/T, ties at the threshold really happen
@@ -356,6 +375,80 @@ def test_G2_easy_label_forest_bitwise_vs_sklearn(ccfd):
     Xn[::7, 3] = np.nan
     assert np.array_equal(bits(_score_device(forest, Xn, "stream")), bits(rf.predict_proba(Xn)))
     forest.close()
+
+
+def test_G3_configs2_forest_500_unbounded_trees_1M_rows_vs_sklearn_digest(ccfd):
+    """BASELINE configs[2] at full model size: 500 trees of unbounded depth (13.4 M
+    nodes, depth 29-40, 107 MB packed, blob offsets in the millions) refitted here from the seeds, 1 M
+    rows scored through `auto` (GLOBAL kernel, with and without the row pre-sort) from device pointers and
+    through the chunked host-pointer path, compared with the digests of scikit-learn's own
+    predict_proba(n_jobs=1) committed by tests/golden/make_golden.py --g3 (per 100k-row slice, so a
+    mismatch names its slice), plus the first 4,096 probability pairs bit by bit."""
+    import sys
+
+    sys.path.insert(0, GOLDEN_DIR)
+    import make_golden
+
+    from ccfd_demo_summit_b200 import converter
+
+    _, model = ccfd
+    with open(os.path.join(GOLDEN_DIR, "g_full_hashes.json")) as fh:
+        g = json.load(fh)["G3_unbounded"]
+    head = np.load(os.path.join(GOLDEN_DIR, "g3_head.npy"))
+    rf, Xq = make_golden.g3_forest_and_rows()
+    assert hashlib.sha256(Xq.tobytes()).hexdigest() == g["X_sha256"]
+    nodes = [int(e.tree_.node_count) for e in rf.estimators_]
+    assert sum(nodes) == g["n_nodes"], "the refitted forest differs from the one the digest was taken from"
+    forest = model.Forest(converter.from_sklearn(rf))
+    del rf
+    assert forest.info["stream_kernel_ok"] == 0 and forest.info["n_trees"] == g["trees"]
+
+    def check(got, what):
+        assert np.array_equal(bits(got[:4096]), bits(head)), what
+        for i, want in enumerate(g["P_sha256_per_100k"]):
+            sl = np.ascontiguousarray(got[i * 100_000:(i + 1) * 100_000])
+            assert hashlib.sha256(sl.tobytes()).hexdigest() == want, (what, "slice", i)
+        assert hashlib.sha256(np.ascontiguousarray(got).tobytes()).hexdigest() == g["P_sha256"], what
+        assert int((got[:, 1] > 0.5).sum()) == g["fraud_gt_0.5"] and int((got[:, 1] >= 0.5).sum()) == g["fraud_ge_0.5"]
+
+    check(_score_device(forest, Xq, "auto"), "device pointers, auto")
+    check(forest.predict_proba(Xq), "host pointers, chunked")
+    os.environ["CCFD_ROW_SORT"] = "0"
+    try:
+        check(_score_device(forest, Xq, "global"), "device pointers, arrival order")
+    finally:
+        del os.environ["CCFD_ROW_SORT"]
+    d = forest.decide(Xq, 0.5, ge=True)
+    assert int(d.sum()) == g["fraud_ge_0.5"]
+    forest.close()
+
+
+def test_session_request_overtakes_queued_bulk_batches(full_forest):
+    """configs[4]: a single-transaction request (jBPM/Camel pattern, reference deploy/ccd-service.yaml:61-66)
+    submitted BEHIND a queue of bulk batches completes before they do: session streams have the highest
+    priority and the bulk kernel's CTAs yield between batches."""
+    from ccfd_demo_summit_b200 import model
+
+    X, rf, forest = full_forest
+    n = 2_000_000
+    xs = torch.from_numpy(np.tile(X, (8, 1))[:n]).cuda()
+    out = torch.empty((n, 2), dtype=torch.float64, device="cuda")
+    sess = model.Session(forest, 1024, 2)
+    want = rf.predict_proba(X[:1])
+    sess.score(0, X[:1])  # warm
+    bulk = torch.cuda.Stream()
+    done = torch.cuda.Event()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(bulk):
+        for _ in range(40):  # ~45 ms of queued bulk work
+            forest.predict_proba_device(xs.data_ptr(), n, 30, out.data_ptr(), bulk.cuda_stream, "stream", sync=False)
+        done.record(bulk)
+    got = sess.score(0, X[:1])
+    still_running = not done.query()
+    torch.cuda.synchronize()
+    assert np.array_equal(bits(got), bits(want))
+    assert still_running, "the request waited for the whole bulk queue"
+    sess.close()
 
 
 def test_multi_gpu_row_sharding_in_one_process(full_forest):

@@ -304,3 +304,129 @@ def test_coalesced_single_transaction_requests_on_the_gpu():
     assert np.array_equal(bits(np.concatenate(out)), bits(P[:64]))
     assert co.launches < 64
     m.close()
+
+
+def test_metrics_registry_exposition_is_prometheus_text():
+    from ccfd_demo_summit_b200 import metrics
+
+    reg = metrics.Registry()
+    reg.declare("ccfd_requests_total", "counter")
+    reg.declare("ccfd_score_seconds", "histogram", metrics.LATENCY_BUCKETS)
+
+    def work():
+        for _ in range(100):
+            reg.inc("ccfd_requests_total", 1, path="session")
+            reg.observe("ccfd_score_seconds", 30e-6, path="session")
+            reg.observe("ccfd_score_seconds", 0.5, path="session")
+
+    th = [threading.Thread(target=work) for _ in range(4)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    txt = reg.exposition()
+    assert '# TYPE ccfd_requests_total counter' in txt and 'ccfd_requests_total{path="session"} 400' in txt
+    assert 'ccfd_score_seconds_bucket{le="5e-05",path="session"} 400' in txt   # cumulative
+    assert 'ccfd_score_seconds_bucket{le="+Inf",path="session"} 800' in txt
+    assert 'ccfd_score_seconds_count{path="session"} 800' in txt
+
+
+@pytest.mark.gpu
+def test_prometheus_endpoint_carries_model_counters_and_seldon_request_histograms():
+    """besides the four gauges, batch-size / scoring-time histograms and the request
+    families the SeldonCore board plots (reference deploy/grafana/SeldonCore.json:119,499-531)."""
+    _, m, X, P = _model()
+    app = sh.SeldonApp(m)
+    for n in (1, 7, 300, 900):
+        code, _ = app.serve(json.dumps({"data": {"ndarray": X[:n].astype(np.float64).tolist()}}).encode())
+        assert code == 200
+    code, _ = app.serve(b'{"data":{"ndarray":[[1,2,3]]}}')
+    assert code == 400
+    txt = sh.prometheus_text(m, app.registry)
+    for name in ("# TYPE proba_1 gauge", "# TYPE ccfd_requests_total counter", 'ccfd_requests_total{path="session"} 3',
+                 'ccfd_requests_total{path="bulk"} 1', 'ccfd_rows_total{path="bulk"} 900', "# TYPE ccfd_request_rows histogram",
+                 'ccfd_request_rows_bucket{le="8"} 2', "# TYPE ccfd_score_seconds histogram", "ccfd_predict_seconds_count",
+                 "# TYPE seldon_api_engine_server_requests_seconds histogram", "seldon_api_engine_client_requests_seconds_bucket{"):
+        assert name in txt, name
+    assert 'seldon_api_engine_server_requests_seconds_count{deployment_name="modelfull"' in txt
+    assert 'status="400"} 1' in txt and 'status="200"} 4' in txt
+    app.close()
+    m.close()
+
+
+@pytest.mark.gpu
+def test_concurrent_predict_calls_overlap_on_different_slots():
+    """n_slots requests are in flight at once: no lock is held around copy-in + graph + wait."""
+    from ccfd_demo_summit_b200 import converter, model
+
+    raw, X, P, _ = load_golden("small_hard")
+    fa = converter.from_arrays(raw.tree_offsets, raw.left, raw.right, raw.feature, raw.threshold,
+                               raw.missing_go_to_left, raw.value, raw.n_features, raw.n_classes)
+    m = model.CcfdForestModel(fa, session_max_batch=1024, session_slots=4)
+    X = np.ascontiguousarray(X, dtype=np.float32)
+    errs = []
+
+    def worker(k):
+        try:
+            for i in range(300):
+                lo = (k * 131 + i * 17) % 400
+                got = m.predict(X[lo:lo + 1024], None)
+                if not np.array_equal(bits(got), bits(P[lo:lo + 1024])):
+                    raise AssertionError((k, i))
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in range(8)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs, errs[:1]
+    assert m.max_in_flight > 1, "requests never overlapped"
+    x_last, p_last = m._last
+    assert np.array_equal(bits(m.predict(x_last[None, :])[0]), bits(p_last))  # the gauge's row and probability belong together
+    m.close()
+
+
+@pytest.mark.gpu
+def test_native_batcher_binary_records_replay_and_inf_refusal():
+    from ccfd_demo_summit_b200 import _lib
+
+    model, m, X, P = _model()
+    sess = model.Session(m.forest, max_batch=256, n_slots=3)
+    got = np.full((1500, 2), np.nan)
+    lats = []
+
+    def on_result(first, probs, lat):
+        got[first:first + len(probs)] = probs
+        lats.append(lat)
+
+    mb = ingest.MicroBatcher(sess, batch=256, on_result=on_result)
+    for i in range(0, 1500, 97):       # binary records in polls of 97
+        mb.push_rows(X[i:i + 97])
+    mb.close()
+    assert mb.batches == 6 and np.array_equal(bits(got), bits(P[:1500]))
+    assert all(0 < v < 1.0 for v in lats)
+    # native replay at a fixed rate with a consumer thread collecting results
+    got[:] = np.nan
+    lats.clear()
+    mb = ingest.MicroBatcher(sess, batch=256, on_result=on_result)
+    t = threading.Thread(target=lambda: mb.replay(X[:1500], records_per_s=2e6, burst=16))
+    t.start()
+    while t.is_alive() or mb.returned < 1500:
+        if mb.drain(200) == 0 and not t.is_alive() and mb.returned >= 1500:
+            break
+    t.join()
+    mb.close()
+    assert np.array_equal(bits(got), bits(P[:1500])) and len(lats) == 6
+    # a record with +-inf is refused, as scikit-learn refuses it
+    mb = ingest.MicroBatcher(sess, batch=256)
+    bad = X[:3].copy()
+    bad[1, 4] = -np.inf
+    with pytest.raises(ValueError, match="infinity"):
+        mb.push_rows(bad)
+    mb.close()
+    with pytest.raises(ValueError, match="2 slots"):
+        ingest.MicroBatcher(model.Session(m.forest, max_batch=64, n_slots=1), batch=64)
+    sess.close()
+    m.close()

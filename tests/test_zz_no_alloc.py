@@ -59,8 +59,10 @@ def test_noalloc_matches_existing_entry_point_on_two_calls_in_a_row():
 
 
 def test_noalloc_rejects_requests_beyond_the_built_in_scratch():
+    from ccfd_demo_summit_b200 import _lib
+
     forest, X, _ = _forest()
-    limit = 1 << 20  # CCFD_NOALLOC_MAX_TREE_ROWS
+    limit = _lib.NOALLOC_MAX_TREE_ROWS  # CCFD_NOALLOC_MAX_TREE_ROWS of include/ccfd_rf.h (kept equal by a CPU test)
     n = limit // forest.n_trees + 1
     xs = torch.zeros((n, 30), dtype=torch.float32, device="cuda")
     out = torch.empty((n, 2), dtype=torch.float64, device="cuda")
@@ -75,4 +77,28 @@ def test_noalloc_rejects_requests_beyond_the_built_in_scratch():
     forest.predict_proba_device(xs.data_ptr(), n, 30, want.data_ptr(), torch.cuda.current_stream().cuda_stream, "stream")
     _noalloc(forest, xs, n, got)
     assert torch.equal(got.view(torch.int64), want.view(torch.int64))
+    forest.close()
+
+
+def test_noalloc_refuses_forests_whose_trees_do_not_fit_shared_memory():
+    """The built-in scratch serves the shared-memory (SPLIT) kernels only: a forest with a tree far
+    beyond a shared-memory stage is answered with CCFD_EUNSUPPORTED, not scored some other way."""
+    from ccfd_demo_summit_b200 import _lib, converter, model
+
+    rng = np.random.default_rng(0)
+    n_int = 9000                          # one comb-shaped tree of 18,001 nodes: > 96 KB packed
+    n = 2 * n_int + 1
+    left = np.full(n, -1, np.int32)
+    right = np.full(n, -1, np.int32)
+    idx = np.arange(n_int) * 2
+    left[idx], right[idx] = idx + 1, idx + 2
+    val = np.tile(np.array([0.25, 0.75]), (n, 1))
+    fa = converter.from_arrays(np.array([0, n]), left, right, rng.integers(0, 30, n), rng.normal(size=n), np.zeros(n, np.uint8),
+                               val, 30, 2)
+    forest = model.Forest(fa)
+    assert forest.info["stream_kernel_ok"] == 0
+    xs = torch.zeros((8, 30), dtype=torch.float32, device="cuda")
+    out = torch.empty((8, 2), dtype=torch.float64, device="cuda")
+    rc = _lib.lib().ccfd_predict_proba_noalloc(forest.handle, ctypes.c_void_p(xs.data_ptr()), 8, 30, ctypes.c_void_p(out.data_ptr()), None)
+    assert rc == _lib.EUNSUPPORTED, _lib.lib().ccfd_last_error()
     forest.close()
