@@ -134,6 +134,7 @@ struct ForestDev {
     uint32_t stage_bytes;    // STREAM ring stage: >= largest blob and >= 128 rows of features
     uint32_t chunk_rows;     // rows of a row chunk that fit a stage, multiple of 32
     uint32_t wide_nodes;     // node encoding: 0 compact, 1 wide (see PackedNode)
+    uint32_t blob_bytes;     // all tree blobs together (0 if beyond 4 GiB): what the forest-resident STREAM variant loads once
 };
 
 // Row pre-sort key (sort.cu): up to 11 features x 2 bits, most used split feature in the top bits.
@@ -152,6 +153,7 @@ struct ccfd_forest {
     std::vector<TreeRec> host_trees;
     std::vector<TopNodes> host_top;
     std::vector<TreeParam> host_params;  // STREAM kernel parameter table (n_trees <= kMaxParamTrees)
+    std::vector<TreeParam> host_params_res;  // the same for the forest-resident variant (absolute offsets)
     int sm_count = 0;
     int smem_optin = 0;
     // host-pointer path: staging owned by the forest, one host call at a time

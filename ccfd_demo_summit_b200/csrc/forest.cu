@@ -346,6 +346,7 @@ static int ccfd_forest_create_impl(const ccfd_forest_desc* d, int device, ccfd_f
     f->dev.n_trees = d->n_trees;
     f->dev.n_features = d->n_features;
     f->dev.max_tree_bytes = max_bytes;
+    f->dev.blob_bytes = blob.size() <= 0xFFFFFFF0ull ? (uint32_t)blob.size() : 0u;
     f->dev.max_depth = max_depth;
 
     f->info.n_trees = d->n_trees;

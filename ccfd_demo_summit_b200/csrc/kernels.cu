@@ -379,18 +379,25 @@ struct RingCursor {
     }
 };
 
-template <int SPT, int TPT, bool TOP, bool XB>
+// RES (forest-resident): a forest small enough to sit in shared memory NEXT to the rows (the Kaggle-like
+// model: 100 trees, 60 KB) is loaded once per CTA and stays; the ring then carries row chunks only, and the
+// tree loop loses its stage waits, stage releases and group bookkeeping.  Needs TOP (per-tree offsets come
+// from the parameter table, here as absolute blob offsets).
+template <int SPT, int TPT, bool TOP, bool XB, bool RES = false>
 __global__ void __launch_bounds__(kStreamThreads, 1)
 k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const int vec_ok, const typename std::conditional<TOP, TopTable, NoTop>::type top) {
+    static_assert(!RES || TOP, "the resident variant takes its per-tree offsets from the parameter table");
     constexpr int S = kConsumerThreads * SPT;
     constexpr int XS = S;
     constexpr int FS = XB ? kBlockRows : XS;  // feature stride of xs in floats
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-    uint64_t* empty = full + kMaxStages;
+    uint64_t* empty = full + kMaxStages;  // [2 * kMaxStages] = 128 bytes; the resident forest's barrier borrows the last slot
+    uint64_t* resbar = empty + kMaxStages - 1;
     const int F = f.n_features;
     const int T = f.n_trees;
     const uint32_t stage_bytes = f.stage_bytes;
+    const uint32_t res_bytes = RES ? round_up(f.blob_bytes, 128u) : 0u;
     // blocked rows start on an 8 KB boundary of the shared window (XBlocked); what the padding
     // costs comes out of the ring
     uint32_t xs_off = 128u, xs_bytes = round_up((uint32_t)(F + 1) * XS * 4u, 128u);
@@ -401,10 +408,12 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
         xs_bytes = (uint32_t)(S / kBlockRows) * kBlockBytes;
         uint32_t total;
         asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(total));
-        n_stages = min(n_stages, (int)((total - xs_off - xs_bytes) / stage_bytes));
+        n_stages = min(n_stages, (int)((total - xs_off - xs_bytes - res_bytes) / stage_bytes));
     }
+    if (RES) n_stages = min(n_stages, kMaxStages - 1);  // the last barrier slot is resbar
     float* xs = reinterpret_cast<float*>(smem + xs_off);
-    uint8_t* ring = smem + xs_off + xs_bytes;
+    uint8_t* resident = smem + xs_off + xs_bytes;  // RES: the whole forest blob, loaded once
+    uint8_t* ring = resident + res_bytes;
     const int tid = threadIdx.x;
     const int64_t n_batches = (a.n + S - 1) / S;
     const int R = (int)f.chunk_rows;  // rows per row chunk, a multiple of 32
@@ -415,6 +424,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
             mbar_init(full + s, 1);
             mbar_init(empty + s, kConsumerWarps);
         }
+        if (RES) mbar_init(resbar, 1);
         mbar_fence_init();
     }
     for (int i = tid; i < S; i += kStreamThreads) xs[(XB ? blocked_row(i) : i) + F * FS] = 0.0f;
@@ -424,6 +434,13 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
         // ---- producer warp: one lane issues every bulk copy of this CTA
         if (tid == kConsumerThreads) {
             RingCursor cur;
+            if (RES) {  // the forest, once: bulk copies of at most 32 KB on one barrier
+                mbar_expect_tx(resbar, f.blob_bytes);
+                for (uint32_t off = 0; off < f.blob_bytes; off += 32768u) {
+                    const uint32_t bytes = min(32768u, f.blob_bytes - off);
+                    bulk_g2s(resident + off, f.blob + off, bytes, resbar);
+                }
+            }
             for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
                 const int64_t row0 = b * S;
                 const bool fast = vec_ok && (a.n - row0 >= (int64_t)S);
@@ -438,7 +455,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
                         cur.advance(n_stages);
                     }
                 }
-                for (int g = 0; g < f.n_groups; ++g) {
+                for (int g = 0; g < (RES ? 0 : f.n_groups); ++g) {
                     const int4 gr = __ldg(reinterpret_cast<const int4*>(f.groups + g));  // GroupRec
                     mbar_wait(empty + cur.stage, cur.phase ^ 1u);
                     mbar_expect_tx(full + cur.stage, (uint32_t)gr.w);
@@ -461,6 +478,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
         xa.XS = XS;
     }
     RingCursor acq, rel;  // next stage to wait for / oldest stage this warp still holds
+    if (RES) mbar_wait(resbar, 0u);
     for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
         const int64_t row0 = b * S;
         const int rows = (int)((a.n - row0) < (int64_t)S ? (a.n - row0) : (int64_t)S);
@@ -497,7 +515,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
 
         // Trees are taken TPT at a time.  A tree's stage is waited for when its group starts and
         // handed back once the group's last tree is done, so a pair may straddle two stages.
-        const uint8_t* gb = nullptr;
+        const uint8_t* gb = RES ? resident : nullptr;
         for (int t0 = 0; t0 < T; t0 += TPT) {
             TreeView tv[TPT];
             int last_of_group[TPT];
@@ -524,7 +542,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
                     tv[k].last_voff = (uint32_t)raw2.y << 4;
                     tv[k].top = nullptr;
                 }
-                if (valid && (depth_flags & 0x10000u)) {  // first tree of a group: its stage must have landed
+                if (!RES && valid && (depth_flags & 0x10000u)) {  // first tree of a group: its stage must have landed
                     mbar_wait(full + acq.stage, acq.phase);
                     gb = ring + (size_t)acq.stage * stage_bytes;
                     acq.advance(n_stages);
@@ -533,7 +551,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
                 tv[k].nodes = smem_u32(tb);
                 tv[k].vals = tv[k].nodes + values_off;
                 tv[k].depth = (int)(depth_flags & 0xFFFFu);
-                last_of_group[k] = valid && (depth_flags & 0x20000u);
+                last_of_group[k] = !RES && valid && (depth_flags & 0x20000u);
             }
             uint32_t voff[TPT][SPT];
             if (TPT == 1 || t0 + TPT <= T) {
@@ -542,14 +560,20 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
                 else
                     descend<SPT, TPT, true, TOP>(tv, xa, voff);
             } else {
-                TreeView one[1] = {tv[0]};
-                uint32_t v1[1][SPT];
-                if (!any_nan)
-                    descend<SPT, 1, false, TOP>(one, xa, v1);
-                else
-                    descend<SPT, 1, true, TOP>(one, xa, v1);
+                // the last, incomplete step: its trees one at a time
 #pragma unroll
-                for (int i = 0; i < SPT; ++i) voff[0][i] = v1[0][i];
+                for (int k = 0; k < TPT - 1; ++k) {
+                    if (t0 + k < T) {
+                        TreeView one[1] = {tv[k]};
+                        uint32_t v1[1][SPT];
+                        if (!any_nan)
+                            descend<SPT, 1, false, TOP>(one, xa, v1);
+                        else
+                            descend<SPT, 1, true, TOP>(one, xa, v1);
+#pragma unroll
+                        for (int i = 0; i < SPT; ++i) voff[k][i] = v1[0][i];
+                    }
+                }
             }
 #pragma unroll
             for (int k = 0; k < TPT; ++k) {
@@ -563,12 +587,14 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
                 }
             }
             // hand back every stage whose last tree was in this step (in ring order)
-            __syncwarp();
+            if constexpr (!RES) {
+                __syncwarp();
 #pragma unroll
-            for (int k = 0; k < TPT; ++k) {
-                if (last_of_group[k]) {
-                    if (lane == 0) mbar_arrive(empty + rel.stage);
-                    rel.advance(n_stages);
+                for (int k = 0; k < TPT; ++k) {
+                    if (last_of_group[k]) {
+                        if (lane == 0) mbar_arrive(empty + rel.stage);
+                        rel.advance(n_stages);
+                    }
                 }
             }
         }
@@ -852,6 +878,21 @@ StreamPlan plan_stream(const ccfd_forest* f, int spt) {
     return p;
 }
 
+// Forest-resident STREAM variant: blocked rows, parameter table, and the whole blob fits beside the rows
+// with at least two row-chunk stages left.
+bool plan_resident(const ccfd_forest* f, int spt, StreamPlan* out) {
+    const bool off = getenv("CCFD_NO_RESIDENT") != nullptr;  // knob for A/B runs and tests (read per launch)
+    if (off || !stream_blocked(f) || f->host_params_res.empty() || f->dev.blob_bytes == 0) return false;
+    const uint32_t S = kConsumerThreads * spt;
+    const int64_t budget = (int64_t)f->smem_optin - 128 - kBlockBytes - (int64_t)(S / kBlockRows) * kBlockBytes - (int64_t)round_up(f->dev.blob_bytes, 128u);
+    if (budget < 2 * (int64_t)f->dev.stage_bytes) return false;
+    out->stage_bytes = f->dev.stage_bytes;
+    out->n_stages = (int)std::min<int64_t>(budget / f->dev.stage_bytes, kMaxStages - 1);
+    out->smem_bytes = (uint32_t)f->smem_optin;
+    out->ok = true;
+    return true;
+}
+
 // SPLIT tile: rows (blocked layout: worst-case padding to the next 8 KB boundary included)
 uint32_t tile_xs_bytes(const ccfd_forest* f, bool blocked) {
     if (blocked) return kBlockBytes + (kTileThreads / kBlockRows) * kBlockBytes;
@@ -880,6 +921,13 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_CUDA(cudaFuncSetAttribute(k_stream<SPT_, TPT_, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));  \
     CCFD_CUDA(cudaFuncSetAttribute(k_stream<SPT_, TPT_, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));  \
     CCFD_CUDA(cudaFuncSetAttribute(k_stream<SPT_, TPT_, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+#define CCFD_RES_ATTRS(SPT_, TPT_) \
+    CCFD_CUDA(cudaFuncSetAttribute(k_stream<SPT_, TPT_, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+    CCFD_RES_ATTRS(1, 2)
+    CCFD_RES_ATTRS(2, 2)
+    CCFD_RES_ATTRS(1, 4)
+    CCFD_RES_ATTRS(2, 4)
+#undef CCFD_RES_ATTRS
     CCFD_STREAM_ATTRS(1, 1)
     CCFD_STREAM_ATTRS(2, 1)
     CCFD_STREAM_ATTRS(1, 2)
@@ -957,6 +1005,12 @@ int ccfd_kernels_init(ccfd_forest* f) {
                 tp.last_vidx = tr.last_vidx;
                 tp.pad = 0;
             }
+            // the same table for the forest-resident variant: absolute blob offsets, no group flags
+            f->host_params_res = f->host_params;
+            for (int t = 0; t < f->dev.n_trees; ++t) {
+                f->host_params_res[(size_t)t].rel_off = f->host_trees[(size_t)t].blob_off16 * 16u;
+                f->host_params_res[(size_t)t].depth_flags = f->host_trees[(size_t)t].depth;
+            }
         }
     }
     return CCFD_OK;
@@ -996,6 +1050,28 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         // two rows per thread (1,024 resident rows per CTA) as soon as 512-row batches would need
         // a second wave: a 1,024-row batch costs ~1.2x a 512-row one, not 2x (more chains in flight)
         int spt = (a.n > (int64_t)f->sm_count * kConsumerThreads) ? 2 : 1;
+        {
+            // small forests: resident variant (the ring carries rows only)
+            StreamPlan rp;
+            int rspt = spt;
+            bool res = plan_resident(f, rspt, &rp);
+            if (!res && rspt == 2) res = plan_resident(f, rspt = 1, &rp);
+            if (res && f->info.stream_kernel_ok) {
+                const int64_t S = (int64_t)kConsumerThreads * rspt;
+                const int64_t n_batches = (a.n + S - 1) / S;
+                const int grid = (int)(n_batches < f->sm_count ? n_batches : f->sm_count);
+                int tpt = 4;
+                if (const char* e = getenv("CCFD_STREAM_TPT")) tpt = atoi(e) == 2 ? 2 : 4;  // tuning knob
+                TopTable top;
+                memcpy(top.t, f->host_params_res.data(), sizeof(TreeParam) * f->host_params_res.size());
+                if (rspt == 2 && tpt == 4) k_stream<2, 4, true, true, true><<<grid, kStreamThreads, rp.smem_bytes, stream>>>(f->dev, a, rp.n_stages, vec_ok, top);
+                else if (rspt == 2) k_stream<2, 2, true, true, true><<<grid, kStreamThreads, rp.smem_bytes, stream>>>(f->dev, a, rp.n_stages, vec_ok, top);
+                else if (tpt == 4) k_stream<1, 4, true, true, true><<<grid, kStreamThreads, rp.smem_bytes, stream>>>(f->dev, a, rp.n_stages, vec_ok, top);
+                else k_stream<1, 2, true, true, true><<<grid, kStreamThreads, rp.smem_bytes, stream>>>(f->dev, a, rp.n_stages, vec_ok, top);
+                CCFD_CUDA(cudaGetLastError());
+                return CCFD_OK;
+            }
+        }
         StreamPlan p = plan_stream(f, spt);
         if (!p.ok && spt == 2) p = plan_stream(f, spt = 1);
         if (!f->info.stream_kernel_ok) p.ok = false;  // no group table was built for this forest

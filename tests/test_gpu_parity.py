@@ -55,6 +55,27 @@ def test_golden_bitwise_device_pointers(ccfd, golden, kernel):
     forest.close()
 
 
+@pytest.mark.parametrize("variant", ["streamed", "resident_tpt2", "resident_tpt4"])
+def test_golden_bitwise_every_stream_variant(ccfd, golden, variant, monkeypatch):
+    """The golden forests are small enough for the forest-resident STREAM variant, which `auto` and
+    `stream` therefore take; the tree-streaming variant (what the 100-tree depth-10 forest runs) and both
+    trees-per-thread settings of the resident one are pinned here explicitly, on small and on 40k-row batches."""
+    _, model = ccfd
+    name, raw, X, P, _ = golden
+    if variant == "streamed":
+        monkeypatch.setenv("CCFD_NO_RESIDENT", "1")
+    else:
+        monkeypatch.setenv("CCFD_STREAM_TPT", variant[-1])
+    forest = model.Forest(_fa(raw))
+    if forest.info["stream_kernel_ok"]:
+        X32 = np.ascontiguousarray(X, dtype=np.float32)
+        assert np.array_equal(bits(_score_device(forest, X32, "stream")), bits(P)), (name, variant)
+        reps = 40_000 // len(X32) + 1
+        big, want = np.tile(X32, (reps, 1))[:40_003], np.tile(P, (reps, 1))[:40_003]  # two rows per thread, ragged tail
+        assert np.array_equal(bits(_score_device(forest, big, "stream")), bits(want)), (name, variant, "40k")
+    forest.close()
+
+
 @pytest.mark.parametrize("kernel", ["stream", "split", "global"])
 def test_strided_and_misaligned_rows(ccfd, kernel):
     _, model = ccfd
