@@ -25,19 +25,44 @@ namespace {
 
 constexpr int kScanBlock = 1024;  // bins per scan block
 
-__global__ void __launch_bounds__(256) k_sort_keys(const float* __restrict__ X, int64_t n, int64_t ld, SortKey sk, int shift,
-                                                   uint32_t* __restrict__ keys, uint32_t* __restrict__ hist) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float* row = X + i * ld;
+__device__ __forceinline__ uint32_t key_bucket(const SortKey& sk, int k, float x) {
+    // NaN compares false everywhere: bucket 0, like any other value it just has to be deterministic
+    return (uint32_t)(x > sk.cut[k][0]) + (uint32_t)(x > sk.cut[k][1]) + (uint32_t)(x > sk.cut[k][2]);
+}
+
+// One warp = 32 consecutive rows.  The rows are read the way they lie in memory (one row per load
+// instruction, lanes = consecutive features: full sectors), parked in shared memory with an odd pitch,
+// and each lane then picks its own row's key features from there.  Wide rows (pitch beyond the shared-memory
+// budget) fall back to strided loads.
+constexpr int kKeyWarps = 8;
+constexpr int kKeyMaxPitch = 65;
+__global__ void __launch_bounds__(kKeyWarps * 32) k_sort_keys(const float* __restrict__ X, int64_t n, int64_t ld, int F, SortKey sk, int shift,
+                                                              uint32_t* __restrict__ keys, uint32_t* __restrict__ hist) {
+    extern __shared__ float rows_s[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t r0 = ((int64_t)blockIdx.x * kKeyWarps + warp) * 32;
+    if (r0 >= n) return;
+    const int64_t i = r0 + lane;
+    const int pitch = F + 1 + (F & 1);  // odd
     uint32_t key = 0;
+    if (pitch <= kKeyMaxPitch) {
+        float* mine = rows_s + warp * 32 * pitch;
+        const int cnt = (int)min((int64_t)32, n - r0);
+        for (int r = 0; r < cnt; ++r) {
+            const float* src = X + (r0 + r) * ld;
+            for (int c = lane; c < F; c += 32) mine[r * pitch + c] = __ldg(src + c);
+        }
+        __syncwarp();
+        if (i < n) {
 #pragma unroll 1
-    for (int k = 0; k < sk.n_feat; ++k) {
-        const float x = __ldg(row + sk.feat[k]);
-        // NaN compares false everywhere: bucket 0, like any other value it just has to be deterministic
-        const uint32_t b = (uint32_t)(x > sk.cut[k][0]) + (uint32_t)(x > sk.cut[k][1]) + (uint32_t)(x > sk.cut[k][2]);
-        key = (key << 2) | b;
+            for (int k = 0; k < sk.n_feat; ++k) key = (key << 2) | key_bucket(sk, k, mine[lane * pitch + sk.feat[k]]);
+        }
+    } else if (i < n) {
+        const float* row = X + i * ld;
+#pragma unroll 1
+        for (int k = 0; k < sk.n_feat; ++k) key = (key << 2) | key_bucket(sk, k, __ldg(row + sk.feat[k]));
     }
+    if (i >= n) return;
     key >>= shift;
     keys[i] = key;
     atomicAdd(hist + key, 1u);
@@ -171,7 +196,9 @@ int ccfd_launch_row_sort(const ccfd_forest* f, const float* X, int64_t n, int64_
     uint32_t* sums = hist + bins;
     CCFD_CUDA(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * (size_t)bins, stream));
     const unsigned grid = (unsigned)((n + 255) / 256);
-    k_sort_keys<<<grid, 256, 0, stream>>>(X, n, ld, f->sort_key, total_bits - bits, keys, hist);
+    const int F = f->dev.n_features, pitch = F + 1 + (F & 1);
+    const size_t key_smem = pitch <= kKeyMaxPitch ? sizeof(float) * kKeyWarps * 32 * (size_t)pitch : 0;
+    k_sort_keys<<<grid, kKeyWarps * 32, key_smem, stream>>>(X, n, ld, F, f->sort_key, total_bits - bits, keys, hist);
     k_scan_block_sums<<<blocks, kScanBlock, 0, stream>>>(hist, bins, sums);
     k_scan_sums<<<1, kScanBlock, 0, stream>>>(sums, blocks);
     k_scan_apply<<<blocks, kScanBlock, 0, stream>>>(hist, bins, sums);

@@ -55,7 +55,7 @@ def test_golden_bitwise_device_pointers(ccfd, golden, kernel):
     forest.close()
 
 
-@pytest.mark.parametrize("variant", ["streamed", "resident_tpt2", "resident_tpt4"])
+@pytest.mark.parametrize("variant", ["streamed", "resident_tpt2", "resident_tpt4", "resident_top1", "resident_top2"])
 def test_golden_bitwise_every_stream_variant(ccfd, golden, variant, monkeypatch):
     """The golden forests are small enough for the forest-resident STREAM variant, which `auto` and
     `stream` therefore take; the tree-streaming variant (what the 100-tree depth-10 forest runs) and both
@@ -64,8 +64,10 @@ def test_golden_bitwise_every_stream_variant(ccfd, golden, variant, monkeypatch)
     name, raw, X, P, _ = golden
     if variant == "streamed":
         monkeypatch.setenv("CCFD_NO_RESIDENT", "1")
-    else:
+    elif "tpt" in variant:
         monkeypatch.setenv("CCFD_STREAM_TPT", variant[-1])
+    else:
+        monkeypatch.setenv("CCFD_RES_TOP", variant[-1])  # levels walked from the parameter table
     forest = model.Forest(_fa(raw))
     if forest.info["stream_kernel_ok"]:
         X32 = np.ascontiguousarray(X, dtype=np.float32)
@@ -373,6 +375,27 @@ def test_G1_full_batch_bitwise_vs_sklearn_on_this_box(full_forest):
     assert int((got[:, 1] > 0.5).sum()) == g["fraud_at_0.5"]
     got = _score_device(forest, X[:5000], "split")
     assert np.array_equal(bits(got), bits(P[:5000]))
+
+
+def test_presorted_stream_launch_changes_no_bit(full_forest, monkeypatch):
+    """The tree-streaming kernel behind the row pre-sort (rows fetched one 128-byte window each through the
+    permutation, results scattered back): same bits as arrival order and as scikit-learn, for even and odd
+    row counts (an odd count scores the last row by a launch of its own), ragged batches and NaN rows."""
+    X, rf, forest = full_forest
+    monkeypatch.setenv("CCFD_STREAM_SORT_MIN", "1")
+    P = rf.predict_proba(X[:70_001])
+    for n in (70_001, 70_000, 2048, 2047, 1025, 1024, 33, 2, 1):
+        got = _score_device(forest, X[:n], "stream")
+        assert np.array_equal(bits(got), bits(P[:n])), n
+    Xn = X[:50_001].copy()
+    Xn[::7, 3] = np.nan
+    Xn[5::11, 17] = np.nan
+    assert np.array_equal(bits(_score_device(forest, Xn, "stream")), bits(rf.predict_proba(Xn)))
+    # strided / misaligned rows cannot take the windowed fetch: they fall back to arrival order, same bits
+    assert np.array_equal(bits(_score_device(forest, X[:5000], "stream", ld=37)), bits(P[:5000]))
+    assert np.array_equal(bits(_score_device(forest, X[:5000], "stream", misalign=True)), bits(P[:5000]))
+    d = forest.decide(X[:70_001], 0.5, ge=False, kernel="stream")
+    assert np.array_equal(d, P[:, 1] > 0.5)
 
 
 def test_G2_easy_label_forest_bitwise_vs_sklearn(ccfd):
