@@ -41,24 +41,12 @@ int enqueue_device(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel, cu
     int rc = CCFD_OK;
     if (kernel == CCFD_KERNEL_SPLIT) {
         CCFD_CUDA(cudaMallocAsync(&scratch, (size_t)ccfd_split_scratch_bytes(f, a.n), stream));
-    } else if (ccfd_row_sort_wanted(f, kernel, a)) {
-        // Bulk launch: order the rows first so that a warp's rows share tree paths (sort.cu).  The STREAM
-        // kernel fetches a pre-sorted row as the 128-byte aligned window around it; for an even row index
-        // that window ends 8 bytes past the row, so with an odd row count the last row of X is kept out of
-        // the sorted launch and scored by a one-row launch of its own (nothing is read past the end of X).
-        if (kernel == CCFD_KERNEL_STREAM && (a.n & 1)) args.n = a.n - 1;
-        CCFD_CUDA(cudaMallocAsync(&scratch, (size_t)ccfd_sort_scratch_bytes(f, args.n), stream));
-        rc = ccfd_launch_row_sort(f, args.X, args.n, args.ld, scratch, &args.perm, stream);
+    } else if (ccfd_row_sort_wanted(f, kernel, a.n)) {
+        // bulk GLOBAL launch: order the rows first so that a warp's rows share tree paths (sort.cu)
+        CCFD_CUDA(cudaMallocAsync(&scratch, (size_t)ccfd_sort_scratch_bytes(f, a.n), stream));
+        rc = ccfd_launch_row_sort(f, a.X, a.n, a.ld, scratch, &args.perm, stream);
     }
     if (rc == CCFD_OK) rc = ccfd_launch_score(f, args, kernel, scratch, stream);
-    if (rc == CCFD_OK && args.n != a.n) {
-        ScoreArgs last = a;
-        last.X = a.X + (a.n - 1) * a.ld;
-        last.n = 1;
-        last.out = a.out ? a.out + 2 * (a.n - 1) : nullptr;
-        last.decision = a.decision ? a.decision + (a.n - 1) : nullptr;
-        rc = ccfd_launch_score(f, last, CCFD_KERNEL_STREAM, nullptr, stream);
-    }
     if (scratch) {
         cudaError_t e = cudaFreeAsync(scratch, stream);
         if (rc == CCFD_OK && e != cudaSuccess) return ccfd_cuda_fail(e, "cudaFreeAsync");
@@ -335,10 +323,7 @@ extern "C" int ccfd_kernel_for(const ccfd_forest* f, int64_t n, uint32_t* kernel
     return ccfd_guarded("ccfd_kernel_for", [&]() -> int {
         if (!f || !kernel) return ccfd_fail(CCFD_EINVAL, "null argument");
         *kernel = ccfd_pick_kernel(f, n);
-        if (rows_presorted) {  // as a dense, aligned device-pointer call of that size would be treated
-            ScoreArgs probe{reinterpret_cast<const float*>(uintptr_t(256)), n, f->dev.n_features, nullptr, nullptr, 0.5, 0};
-            *rows_presorted = ccfd_row_sort_wanted(f, *kernel, probe) ? 1 : 0;
-        }
+        if (rows_presorted) *rows_presorted = ccfd_row_sort_wanted(f, *kernel, n) ? 1 : 0;
         return CCFD_OK;
     });
 }

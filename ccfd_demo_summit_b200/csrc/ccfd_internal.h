@@ -237,7 +237,7 @@ struct ScoreArgs {
     uint8_t* decision;  // device, may be null
     double threshold;
     int ge;
-    const uint32_t* perm = nullptr;  // device, optional (GLOBAL kernel, pre-sorted STREAM launches): row i of the launch is row perm[i] of X / out / decision
+    const uint32_t* perm = nullptr;  // device, optional (GLOBAL kernel): row i of the launch is row perm[i] of X / out / decision
 };
 
 // Pick + launch.  `kernel` is one of CCFD_KERNEL_*; scratch is used by SPLIT only
@@ -253,4 +253,4 @@ void ccfd_sort_key_from_desc(const ccfd_forest_desc* d, SortKey* sk);
 int64_t ccfd_sort_scratch_bytes(const ccfd_forest* f, int64_t n);
 int ccfd_launch_row_sort(const ccfd_forest* f, const float* X, int64_t n, int64_t ld, void* scratch, const uint32_t** perm_out,
                          cudaStream_t stream);
-bool ccfd_row_sort_wanted(const ccfd_forest* f, uint32_t kernel, const ScoreArgs& a);
+bool ccfd_row_sort_wanted(const ccfd_forest* f, uint32_t kernel, int64_t n);

@@ -44,8 +44,6 @@ constexpr int kGlobalThreadsBulk = 768;
 constexpr int kGlobalThreadsSmall = 256;
 constexpr int kGlobalThreadsWide = 64;  // rows with so many features that 256 of them overflow shared memory
 constexpr int kSplitStages = 2;
-// bulk STREAM launches from this many rows on are pre-sorted (0 = never); see ccfd_row_sort_wanted
-constexpr int64_t kStreamSortDefaultMin = 0;
 
 __host__ __device__ constexpr uint32_t round_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
 
@@ -367,51 +365,6 @@ __device__ __forceinline__ bool transpose_group(float* __restrict__ xcol, const 
     return nan;
 }
 
-constexpr int kPermFeatures = 30;
-constexpr uint32_t kPermPitch = 144;  // 9 x 16 bytes: LDS.128 of 8 lanes at this stride hit 8 different bank groups
-
-// PERM launches: the lane's row sits in a 128-byte window at `slot` (16-byte aligned), starting at byte 0 or
-// byte 8 of it depending on the parity of the row's index in X (row stride 120 bytes).
-template <int FS>
-__device__ __forceinline__ bool transpose_window(float* __restrict__ xcol, uint32_t slot, bool odd) {
-    float v[32];
-#pragma unroll
-    for (int q = 0; q < 8; ++q) {
-        float4 t;
-        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(slot + 16u * q));
-        v[4 * q] = t.x;
-        v[4 * q + 1] = t.y;
-        v[4 * q + 2] = t.z;
-        v[4 * q + 3] = t.w;
-    }
-    bool nan = false;
-#pragma unroll
-    for (int c = 0; c < kPermFeatures; ++c) {
-        const float x = odd ? v[c + 2] : v[c];
-        xcol[c * FS] = x;
-        nan |= (x != x);
-    }
-    return nan;
-}
-
-// Cooperative tile load through a row permutation (ragged last batch of a PERM launch): a warp copies one
-// row at a time, lanes = consecutive features.
-template <int NT, int S, bool XB>
-__device__ __forceinline__ bool load_tile_perm(float* xs, const float* __restrict__ X, const uint32_t* __restrict__ perm, int rows, int64_t ld, int F, int tid) {
-    auto at = [](int c, int r) { return XB ? ((r >> 6) * 2048 + c * 64 + (r & 63)) : (c * S + r); };
-    bool nan = false;
-    const int lane = tid & 31, warp = tid >> 5;
-    for (int r = warp; r < S; r += NT / 32) {
-        const float* src = r < rows ? X + (int64_t)__ldg(perm + r) * ld : nullptr;
-        for (int c = lane; c < F; c += 32) {
-            const float v = src ? __ldg(src + c) : 0.0f;
-            xs[at(c, r)] = v;
-            nan |= (v != v);
-        }
-    }
-    return nan;
-}
-
 struct TopTable {
     TreeParam t[kMaxParamTrees];
 };
@@ -433,15 +386,10 @@ struct RingCursor {
 // model: 100 trees, 60 KB) is loaded once per CTA and stays; the ring then carries row chunks only, and the
 // tree loop loses its stage waits, stage releases and group bookkeeping.  Needs TOP (per-tree offsets come
 // from the parameter table, here as absolute blob offsets).
-// PERM (pre-sorted launch, csrc/sort.cu): row i of the launch is row perm[i] of X.  The producer warp
-// then fetches every row of a chunk with its own 128-byte bulk copy (the 16-byte aligned window that holds
-// the 120-byte row) into a slot of kPermPitch bytes, the consumers pick the row out of its window while
-// transposing, and results go to out[perm[i]].  Rows of 30 features only (kPermFeatures).
-template <int SPT, int TPT, bool TOP, bool XB, bool RES = false, int TL = kTopLevels, bool PERM = false>
+template <int SPT, int TPT, bool TOP, bool XB, bool RES = false, int TL = kTopLevels>
 __global__ void __launch_bounds__(kStreamThreads, 1)
 k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const int vec_ok, const typename std::conditional<TOP, TopTable, NoTop>::type top) {
     static_assert(!RES || TOP, "the resident variant takes its per-tree offsets from the parameter table");
-    static_assert(!(PERM && RES), "the pre-sorted variant is built for the tree-streaming kernel only");
     constexpr int S = kConsumerThreads * SPT;
     constexpr int XS = S;
     constexpr int FS = XB ? kBlockRows : XS;  // feature stride of xs in floats
@@ -471,7 +419,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
     uint8_t* ring = resident + res_bytes;
     const int tid = threadIdx.x;
     const int64_t n_batches = (a.n + S - 1) / S;
-    const int R = PERM ? (int)(stage_bytes / kPermPitch / 32u * 32u) : (int)f.chunk_rows;  // rows per row chunk, a multiple of 32
+    const int R = (int)f.chunk_rows;  // rows per row chunk, a multiple of 32
     const int n_chunks = (S + R - 1) / R;
 
     if (tid == 0) {
@@ -487,8 +435,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
 
     if (tid >= kConsumerThreads) {
         // ---- producer warp: one lane issues every bulk copy of this CTA
-        if (PERM || tid == kConsumerThreads) {
-            const int plane = tid - kConsumerThreads;  // lane of the producer warp; only lane 0 runs unless PERM
+        if (tid == kConsumerThreads) {
             RingCursor cur;
             if (RES) {  // the forest, once: bulk copies of at most 32 KB on one barrier
                 mbar_expect_tx(resbar, f.blob_bytes);
@@ -500,23 +447,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
             for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
                 const int64_t row0 = b * S;
                 const bool fast = vec_ok && (a.n - row0 >= (int64_t)S);
-                if (fast && PERM) {
-                    for (int c = 0; c < n_chunks; ++c) {
-                        const int r_lo = c * R;
-                        const int r_n = (S - r_lo) < R ? (S - r_lo) : R;
-                        if (plane == 0) {
-                            mbar_wait(empty + cur.stage, cur.phase ^ 1u);
-                            mbar_expect_tx(full + cur.stage, (uint32_t)r_n * 128u);
-                        }
-                        __syncwarp();
-                        uint8_t* dst = ring + (size_t)cur.stage * stage_bytes;
-                        for (int r = plane; r < r_n; r += 32) {
-                            const uint64_t o = (uint64_t)__ldg(a.perm + row0 + r_lo + r) * (uint64_t)(kPermFeatures * 4);
-                            bulk_g2s(dst + (uint32_t)r * kPermPitch, reinterpret_cast<const uint8_t*>(a.X) + (o & ~(uint64_t)15), 128u, full + cur.stage);
-                        }
-                        cur.advance(n_stages);
-                    }
-                } else if (fast) {
+                if (fast) {
                     for (int c = 0; c < n_chunks; ++c) {
                         const int r_lo = c * R;
                         const int r_n = (S - r_lo) < R ? (S - r_lo) : R;
@@ -526,10 +457,6 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
                         bulk_g2s(ring + (size_t)cur.stage * stage_bytes, a.X + (row0 + r_lo) * (int64_t)F, bytes, full + cur.stage);
                         cur.advance(n_stages);
                     }
-                }
-                if (PERM && plane != 0) {  // tree groups are lane 0's; the other lanes only keep their cursor in step
-                    for (int g = 0; g < f.n_groups; ++g) cur.advance(n_stages);
-                    continue;
                 }
                 for (int g = 0; g < (RES ? 0 : f.n_groups); ++g) {
                     const int4 gr = __ldg(reinterpret_cast<const int4*>(f.groups + g));  // GroupRec
@@ -570,12 +497,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
                 for (int lg = (warp - c * k) & (kConsumerWarps - 1); lg < cnt; lg += kConsumerWarps) {
                     const int i = (c * k + lg) / kConsumerWarps;  // which of this thread's SPT rows
                     const int s = tid + i * kConsumerThreads;
-                    if constexpr (PERM) {
-                        const bool odd = (__ldg(a.perm + row0 + s) & 1u) != 0u;
-                        my_nan |= transpose_window<FS>(xs + (XB ? blocked_row(s) : s), smem_u32(chunk) + (uint32_t)(lg * 32 + lane) * kPermPitch, odd);
-                    } else {
-                        my_nan |= transpose_group<FS>(xs + (XB ? blocked_row(s) : s), chunk + (size_t)lg * 32 * F, F, lane);
-                    }
+                    my_nan |= transpose_group<FS>(xs + (XB ? blocked_row(s) : s), chunk + (size_t)lg * 32 * F, F, lane);
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(empty + acq.stage);
@@ -586,11 +508,7 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
         } else {
             // ragged last batch, strided or unaligned rows: cooperative load with block barriers
             named_bar_sync(1, kConsumerThreads);
-            bool my_nan;
-            if constexpr (PERM)
-                my_nan = load_tile_perm<kConsumerThreads, S, XB>(xs, a.X, a.perm + row0, rows, a.ld, F, tid);
-            else
-                my_nan = load_tile<kConsumerThreads, S, XB>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
+            const bool my_nan = load_tile<kConsumerThreads, S, XB>(xs, a.X + row0 * a.ld, rows, a.ld, F, vec_ok != 0, tid);
             any_nan = named_bar_or(2, kConsumerThreads, my_nan);
         }
 
@@ -688,9 +606,8 @@ k_stream(const ForestDev f, const ScoreArgs a, const int n_stages_planned, const
             const int s = tid + i * kConsumerThreads;
             if (s < rows) {
                 const double p0 = acc0[i] / Td, p1 = acc1[i] / Td;  // true divide: SK/ensemble/_forest.py:962
-                const int64_t dst = PERM ? (int64_t)__ldg(a.perm + row0 + s) : row0 + s;
-                if (a.out) reinterpret_cast<double2*>(a.out)[dst] = make_double2(p0, p1);
-                if (a.decision) a.decision[dst] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
+                if (a.out) reinterpret_cast<double2*>(a.out)[row0 + s] = make_double2(p0, p1);
+                if (a.decision) a.decision[row0 + s] = (uint8_t)(a.ge ? (p1 >= a.threshold) : (p1 > a.threshold));
             }
         }
     }
@@ -1016,7 +933,6 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_RES_ATTRS(1, 4)
     CCFD_RES_ATTRS(2, 4)
 #undef CCFD_RES_ATTRS
-    CCFD_CUDA(cudaFuncSetAttribute(k_stream<2, 2, true, true, false, kTopLevels, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
     CCFD_STREAM_ATTRS(1, 1)
     CCFD_STREAM_ATTRS(2, 1)
     CCFD_STREAM_ATTRS(1, 2)
@@ -1105,37 +1021,18 @@ int ccfd_kernels_init(ccfd_forest* f) {
     return CCFD_OK;
 }
 
-// Can this STREAM launch take its rows through a permutation?  (the PERM instantiation: tree-streaming
-// kernel, two rows and two trees per thread, parameter table, blocked 30-feature rows, dense aligned X)
-static bool stream_perm_ok(const ccfd_forest* f, const ScoreArgs& a) {
-    if (!f->info.stream_kernel_ok || f->dev.n_features != kPermFeatures || f->host_params.empty() || !stream_blocked(f)) return false;
-    if (a.ld != kPermFeatures || (reinterpret_cast<uintptr_t>(a.X) & 15u)) return false;
-    StreamPlan rp;
-    if (plan_resident(f, 2, &rp) || plan_resident(f, 1, &rp)) return false;
-    const StreamPlan p = plan_stream(f, 2);
-    return p.ok && (p.n_stages >= 4 || 2 * f->dev.n_groups <= f->dev.n_trees) && f->dev.stage_bytes / kPermPitch >= 32u;
-}
-
-// The row pre-sort (sort.cu) pays where a warp's rows sharing tree paths saves memory wavefronts and the
-// launch is long enough to hide it: always for bulk GLOBAL launches (node loads through L1/L2), and for
-// bulk STREAM launches of the tree-streaming kernel (fewer shared-memory bank conflicts).  CCFD_ROW_SORT=0
-// switches it off (A/B runs, tests), CCFD_ROW_SORT_MIN / CCFD_STREAM_SORT_MIN move the thresholds.
-bool ccfd_row_sort_wanted(const ccfd_forest* f, uint32_t kernel, const ScoreArgs& a) {
-    if (f->sort_key.n_feat < 4 || a.n > 0xFFFFFFFFll || a.perm) return false;
+// The row pre-sort (sort.cu) pays where node loads go through L1/L2 and the launch is long enough to hide
+// it: bulk GLOBAL launches.  (For the shared-memory STREAM kernel it was built and measured, and does not
+// pay: DESIGN.md section 5.)  CCFD_ROW_SORT=0 switches it off (A/B runs, tests), CCFD_ROW_SORT_MIN moves the
+// threshold.
+bool ccfd_row_sort_wanted(const ccfd_forest* f, uint32_t kernel, int64_t n) {
+    if (kernel != CCFD_KERNEL_GLOBAL || f->sort_key.n_feat < 4 || n > 0xFFFFFFFFll) return false;
+    int64_t min_rows = 262144;
     if (const char* e = getenv("CCFD_ROW_SORT")) {  // read per call: a knob for experiments, not a hot path
         if (atoi(e) == 0) return false;
     }
-    if (kernel == CCFD_KERNEL_GLOBAL) {
-        int64_t min_rows = 262144;
-        if (const char* e = getenv("CCFD_ROW_SORT_MIN")) min_rows = atoll(e);
-        return a.n >= min_rows;
-    }
-    if (kernel == CCFD_KERNEL_STREAM) {
-        int64_t min_rows = kStreamSortDefaultMin;
-        if (const char* e = getenv("CCFD_STREAM_SORT_MIN")) min_rows = atoll(e);
-        return min_rows > 0 && a.n >= std::max<int64_t>(min_rows, 2) && stream_perm_ok(f, a);
-    }
-    return false;
+    if (const char* e = getenv("CCFD_ROW_SORT_MIN")) min_rows = atoll(e);
+    return n >= std::max<int64_t>(min_rows, 1);
 }
 
 uint32_t ccfd_pick_kernel(const ccfd_forest* f, int64_t n) {
@@ -1154,19 +1051,7 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
     if (reinterpret_cast<uintptr_t>(a.X) & 3u) return ccfd_fail(CCFD_EINVAL, "X must be 4-byte aligned");
     const int vec_ok = (a.ld == f->dev.n_features) && ((reinterpret_cast<uintptr_t>(a.X) & 15u) == 0);
     if (kernel == CCFD_KERNEL_AUTO) kernel = ccfd_pick_kernel(f, a.n);
-    if (a.perm && kernel == CCFD_KERNEL_SPLIT) return ccfd_fail(CCFD_EINVAL, "internal: the SPLIT kernel takes no row permutation");
-    if (a.perm && kernel == CCFD_KERNEL_STREAM) {
-        if (!stream_perm_ok(f, a)) return ccfd_fail(CCFD_EINVAL, "internal: this STREAM launch cannot take a row permutation");
-        const StreamPlan p = plan_stream(f, 2);
-        const int64_t S = (int64_t)kConsumerThreads * 2;
-        const int64_t n_batches = (a.n + S - 1) / S;
-        const int grid = (int)(n_batches < f->sm_count ? n_batches : f->sm_count);
-        TopTable top;
-        memcpy(top.t, f->host_params.data(), sizeof(TreeParam) * f->host_params.size());
-        k_stream<2, 2, true, true, false, kTopLevels, true><<<grid, kStreamThreads, p.smem_bytes, stream>>>(f->dev, a, p.n_stages, 1, top);
-        CCFD_CUDA(cudaGetLastError());
-        return CCFD_OK;
-    }
+    if (a.perm && kernel != CCFD_KERNEL_GLOBAL) return ccfd_fail(CCFD_EINVAL, "internal: a row permutation is only understood by the GLOBAL kernel");
 
     if (kernel == CCFD_KERNEL_STREAM) {
         // two rows per thread (1,024 resident rows per CTA) as soon as 512-row batches would need

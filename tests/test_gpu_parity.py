@@ -377,27 +377,6 @@ def test_G1_full_batch_bitwise_vs_sklearn_on_this_box(full_forest):
     assert np.array_equal(bits(got), bits(P[:5000]))
 
 
-def test_presorted_stream_launch_changes_no_bit(full_forest, monkeypatch):
-    """The tree-streaming kernel behind the row pre-sort (rows fetched one 128-byte window each through the
-    permutation, results scattered back): same bits as arrival order and as scikit-learn, for even and odd
-    row counts (an odd count scores the last row by a launch of its own), ragged batches and NaN rows."""
-    X, rf, forest = full_forest
-    monkeypatch.setenv("CCFD_STREAM_SORT_MIN", "1")
-    P = rf.predict_proba(X[:70_001])
-    for n in (70_001, 70_000, 2048, 2047, 1025, 1024, 33, 2, 1):
-        got = _score_device(forest, X[:n], "stream")
-        assert np.array_equal(bits(got), bits(P[:n])), n
-    Xn = X[:50_001].copy()
-    Xn[::7, 3] = np.nan
-    Xn[5::11, 17] = np.nan
-    assert np.array_equal(bits(_score_device(forest, Xn, "stream")), bits(rf.predict_proba(Xn)))
-    # strided / misaligned rows cannot take the windowed fetch: they fall back to arrival order, same bits
-    assert np.array_equal(bits(_score_device(forest, X[:5000], "stream", ld=37)), bits(P[:5000]))
-    assert np.array_equal(bits(_score_device(forest, X[:5000], "stream", misalign=True)), bits(P[:5000]))
-    d = forest.decide(X[:70_001], 0.5, ge=False, kernel="stream")
-    assert np.array_equal(d, P[:, 1] > 0.5)
-
-
 def test_G2_easy_label_forest_bitwise_vs_sklearn(ccfd):
     """Kaggle-like forest (0.17 % positives, separable): tens of nodes per tree, trees of very
     different depths, many trees per shared-memory stage."""
