@@ -46,6 +46,7 @@ SYMBOLS = [
     ("ccfd_predict_proba", c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_uint32, c_void_p]),
     ("ccfd_predict_decision", c_int,
      [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_double, c_int, c_uint32, c_void_p]),
+    ("ccfd_predict_proba_rows", c_int, [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_void_p, c_uint32, POINTER(c_int32)]),
     ("ccfd_kernel_for", c_int, [c_void_p, c_int64, POINTER(c_uint32), POINTER(c_int32)]),
     ("ccfd_predict_proba_noalloc", c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     ("ccfd_session_create", c_int, [c_void_p, c_int64, c_int32, POINTER(c_void_p)]),

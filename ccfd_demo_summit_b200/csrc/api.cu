@@ -54,6 +54,99 @@ int enqueue_device(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel, cu
     return rc;
 }
 
+constexpr int64_t kPageableChunkRows = 65536;  // 7.5 MB of fp32 rows per pipeline step
+
+int ensure_pinned(ccfd_forest* f, int64_t rows) {
+    if (f->pin_rows >= rows) return CCFD_OK;
+    for (int i = 0; i < 2; ++i) {
+        if (f->stage_stream[i]) CCFD_CUDA(cudaStreamSynchronize(f->stage_stream[i]));
+        cudaFreeHost(f->pin_x[i]);
+        cudaFreeHost(f->pin_p[i]);
+        cudaFreeHost(f->pin_d[i]);
+        f->pin_x[i] = nullptr;
+        f->pin_p[i] = nullptr;
+        f->pin_d[i] = nullptr;
+    }
+    f->pin_rows = 0;
+    for (int i = 0; i < 2; ++i) {
+        CCFD_CUDA(cudaHostAlloc(&f->pin_x[i], sizeof(float) * (size_t)rows * (size_t)f->dev.n_features, cudaHostAllocDefault));
+        CCFD_CUDA(cudaHostAlloc(&f->pin_p[i], sizeof(double) * 2 * (size_t)rows, cudaHostAllocDefault));
+        CCFD_CUDA(cudaHostAlloc(&f->pin_d[i], (size_t)rows, cudaHostAllocDefault));
+    }
+    f->pin_rows = rows;
+    return CCFD_OK;
+}
+
+// Rows in PAGEABLE host memory (what a Seldon wrapper hands predict(): a numpy matrix, float64 after JSON
+// decoding or float32).  A cudaMemcpyAsync from pageable memory is staged by the driver on one thread; here
+// the library does the staging itself, fused with the float64 -> float32 narrowing and the infinity scan of
+// ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625), on its host thread pool, two
+// pinned buffers deep: while the GPU copies in, scores and copies out chunk k, the CPU casts chunk k+1 and
+// hands chunk k-1's results to the caller's array.  *has_inf (may be null) reports +-inf / float32 overflow
+// in the input; scoring stops at the chunk that holds it.
+int score_pageable(ccfd_forest* f, const void* X, int32_t is_f64, int64_t n, int64_t ld, double* out, uint8_t* decision, double threshold,
+                   int ge, uint32_t kernel, int32_t* has_inf) {
+    std::lock_guard<std::mutex> lock(f->host_mu);
+    const int F = f->dev.n_features;
+    const int64_t chunk = std::min<int64_t>(n, kPageableChunkRows);
+    int rc = ensure_staging(f, chunk);
+    if (rc == CCFD_OK) rc = ensure_pinned(f, chunk);
+    if (rc != CCFD_OK) return rc;
+    if (has_inf) *has_inf = 0;
+    struct InFlight {
+        int64_t r0 = 0, rows = 0;
+        bool live = false;
+    } fl[2];
+    auto finish = [&](int s) -> int {  // wait for slot s and hand its results over
+        if (!fl[s].live) return CCFD_OK;
+        fl[s].live = false;
+        CCFD_CUDA(cudaStreamSynchronize(f->stage_stream[s]));
+        if (out) memcpy(out + 2 * fl[s].r0, f->pin_p[s], sizeof(double) * 2 * (size_t)fl[s].rows);
+        if (decision) memcpy(decision + fl[s].r0, f->pin_d[s], (size_t)fl[s].rows);
+        return CCFD_OK;
+    };
+    int k = 0;
+    for (int64_t r0 = 0; r0 < n && rc == CCFD_OK; r0 += chunk, ++k) {
+        const int s = k & 1;
+        const int64_t rows = std::min<int64_t>(chunk, n - r0);
+        rc = finish(s);  // chunk k-2 used this slot
+        if (rc != CCFD_OK) break;
+        int32_t bad = 0;
+        const void* src = is_f64 ? static_cast<const void*>(static_cast<const double*>(X) + r0 * ld)
+                                 : static_cast<const void*>(static_cast<const float*>(X) + r0 * ld);
+        rc = ccfd_cast_span(src, is_f64, rows, F, ld, f->pin_x[s], &bad);
+        if (rc != CCFD_OK) break;
+        if (bad && has_inf) {
+            *has_inf = 1;
+            break;
+        }
+        cudaStream_t st = f->stage_stream[s];
+        CCFD_CUDA(cudaMemcpyAsync(f->stage_x[s], f->pin_x[s], sizeof(float) * (size_t)rows * F, cudaMemcpyHostToDevice, st));
+        ScoreArgs a{f->stage_x[s], rows, F, out ? f->stage_p[s] : nullptr, decision ? f->stage_d[s] : nullptr, threshold, ge};
+        rc = enqueue_device(f, a, kernel, st);
+        if (rc != CCFD_OK) break;
+        if (out) CCFD_CUDA(cudaMemcpyAsync(f->pin_p[s], f->stage_p[s], sizeof(double) * 2 * (size_t)rows, cudaMemcpyDeviceToHost, st));
+        if (decision) CCFD_CUDA(cudaMemcpyAsync(f->pin_d[s], f->stage_d[s], (size_t)rows, cudaMemcpyDeviceToHost, st));
+        fl[s].r0 = r0;
+        fl[s].rows = rows;
+        fl[s].live = true;
+    }
+    for (int j = 0; j < 2; ++j) {  // oldest first
+        const int rc2 = finish((k + j) & 1);
+        if (rc == CCFD_OK) rc = rc2;
+    }
+    return rc;
+}
+
+bool is_pageable(const void* p) {
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+        cudaGetLastError();
+        return true;
+    }
+    return attr.type == cudaMemoryTypeUnregistered;
+}
+
 int score_impl(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint8_t* decision, double threshold, int ge,
                uint32_t flags, void* stream_) {
     if (!f) return ccfd_fail(CCFD_EINVAL, "null forest");
@@ -80,6 +173,7 @@ int score_impl(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* ou
     // Host rows: chunks alternate between two streams, so the copy-in of chunk k+1 and the
     // copy-out of chunk k-1 overlap the scoring of chunk k.  Every kernel produces the same bits,
     // so results do not depend on how the request is chunked.
+    if (n >= 8192 && is_pageable(X)) return score_pageable(f, X, 0, n, ld, out, decision, threshold, ge, kernel, nullptr);
     std::lock_guard<std::mutex> lock(f->host_mu);
     const int64_t chunk = std::min<int64_t>(n, kHostChunkRows);
     int rc = ensure_staging(f, chunk);
@@ -118,6 +212,23 @@ static int ccfd_predict_decision_impl(ccfd_forest* f, const float* X, int64_t n,
                                      int ge, uint32_t flags, void* stream) {
     if (!decision && n > 0) return ccfd_fail(CCFD_EINVAL, "decision is null");
     return score_impl(f, X, n, ld, out, decision, threshold, ge, flags, stream);
+}
+
+static int ccfd_predict_proba_rows_impl(ccfd_forest* f, const void* X, int32_t x_is_f64, int64_t n, int64_t ld, double* out, uint32_t flags,
+                                        int32_t* has_inf) {
+    if (!f) return ccfd_fail(CCFD_EINVAL, "null forest");
+    if (n < 0) return ccfd_fail(CCFD_EINVAL, "n must be >= 0 (got %lld)", (long long)n);
+    if (has_inf) *has_inf = 0;
+    if (n == 0) return CCFD_OK;
+    if (!X || !out) return ccfd_fail(CCFD_EINVAL, "X and out must not be null");
+    if (ld < f->dev.n_features) return ccfd_fail(CCFD_EINVAL, "row stride %lld is smaller than n_features %d", (long long)ld, f->dev.n_features);
+    if (flags & ~CCFD_KERNEL_MASK) return ccfd_fail(CCFD_EINVAL, "only a kernel selector may be given (host rows, synchronous)");
+    DeviceGuard guard(f->device);
+    int32_t bad = 0;
+    const int rc = score_pageable(f, X, x_is_f64 ? 1 : 0, n, ld, out, nullptr, 0.5, 0, flags & CCFD_KERNEL_MASK, &bad);
+    if (has_inf) *has_inf = bad;
+    if (rc == CCFD_OK && bad) return ccfd_fail(CCFD_EINVAL, "Input X contains infinity or a value too large for dtype('float32').");
+    return rc;
 }
 
 // ===================================================================================== session
@@ -295,6 +406,10 @@ static int ccfd_session_run_impl(ccfd_session* ss, int32_t slot, int64_t n_rows)
 // ---- the C ABI: every body above runs inside ccfd_guarded (no C++ exception crosses the boundary)
 extern "C" int ccfd_predict_proba(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint32_t flags, void* stream) {
     return ccfd_guarded("ccfd_predict_proba", [&]() -> int { return ccfd_predict_proba_impl(f, X, n, ld, out, flags, stream); });
+}
+extern "C" int ccfd_predict_proba_rows(ccfd_forest* f, const void* X, int32_t x_is_f64, int64_t n, int64_t ld, double* out, uint32_t flags,
+                                       int32_t* has_inf) {
+    return ccfd_guarded("ccfd_predict_proba_rows", [&]() -> int { return ccfd_predict_proba_rows_impl(f, X, x_is_f64, n, ld, out, flags, has_inf); });
 }
 extern "C" int ccfd_predict_decision(ccfd_forest* f, const float* X, int64_t n, int64_t ld, double* out, uint8_t* decision, double threshold, int ge, uint32_t flags, void* stream) {
     return ccfd_guarded("ccfd_predict_decision", [&]() -> int { return ccfd_predict_decision_impl(f, X, n, ld, out, decision, threshold, ge, flags, stream); });

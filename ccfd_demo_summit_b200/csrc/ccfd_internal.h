@@ -163,6 +163,11 @@ struct ccfd_forest {
     uint8_t* stage_d[2] = {nullptr, nullptr};
     cudaStream_t stage_stream[2] = {nullptr, nullptr};
     int64_t stage_rows = 0;
+    // pageable-host path: pinned staging the rows are cast / copied into and the results come back to
+    float* pin_x[2] = {nullptr, nullptr};
+    double* pin_p[2] = {nullptr, nullptr};
+    uint8_t* pin_d[2] = {nullptr, nullptr};
+    int64_t pin_rows = 0;
 };
 
 // error plumbing -------------------------------------------------------------------------------
@@ -202,6 +207,8 @@ int ccfd_guarded(const char* where, F&& body) noexcept {
 // caller simply runs every part itself.
 void ccfd_parallel_for(int n_parts, const std::function<void(int)>& fn);
 int ccfd_host_threads();  // parts worth asking for (pool size + the caller), >= 1
+// float64 / float32 rows -> dense float32 rows (dst == null: scan only) + "holds +-inf" (ccfd_cast_rows' body)
+int ccfd_cast_span(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst, int32_t* has_inf);
 
 // Is `dev`'s primary context alive in this process?  (true when the driver cannot be asked)
 bool ccfd_primary_ctx_active(int dev);

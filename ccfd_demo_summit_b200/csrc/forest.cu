@@ -377,6 +377,9 @@ static int ccfd_forest_destroy_impl(ccfd_forest* f) {
         cudaFree(f->stage_p[i]);
         cudaFree(f->stage_d[i]);
         if (f->stage_stream[i]) cudaStreamDestroy(f->stage_stream[i]);
+        cudaFreeHost(f->pin_x[i]);
+        cudaFreeHost(f->pin_p[i]);
+        cudaFreeHost(f->pin_d[i]);
     }
     cudaFree((void*)f->dev.blob);
     cudaFree((void*)f->dev.trees);

@@ -461,64 +461,68 @@ extern "C" int ccfd_format_proba(const double* p, int64_t n_rows, char* dst, int
 // Requests below ~1 M values (every latency-path request) are done on the calling thread: waking other
 // threads costs more than the pass; larger ones go to the persistent host pool (no thread is created
 // per call).
+int ccfd_cast_span(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst, int32_t* has_inf) {
+    constexpr int64_t kValuesPerPart = 1 << 19;
+    const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(ccfd_host_threads(), n * n_cols / kValuesPerPart));
+    std::vector<int> inf_seen((size_t)nt, 0);
+    // spans of contiguous values; +-inf is "exponent all ones, mantissa zero" (NaN is allowed): an integer
+    // test on the bits, which the host compiler vectorises
+    auto is_inf = [](float v) {
+        uint32_t u;
+        memcpy(&u, &v, 4);
+        return (int)((u & 0x7FFFFFFFu) == 0x7F800000u);
+    };
+    auto scan_f32 = [&](const float* sp, int64_t m) {
+        int bad = 0;
+        for (int64_t i = 0; i < m; ++i) bad |= is_inf(sp[i]);
+        return bad;
+    };
+    auto copy_f32 = [&](const float* sp, float* d, int64_t m) {
+        int bad = 0;
+        for (int64_t i = 0; i < m; ++i) {
+            d[i] = sp[i];
+            bad |= is_inf(sp[i]);
+        }
+        return bad;
+    };
+    auto cast_f64 = [&](const double* sp, float* d, int64_t m) {
+        int bad = 0;
+        for (int64_t i = 0; i < m; ++i) {
+            const float v = (float)sp[i];
+            d[i] = v;
+            bad |= is_inf(v);
+        }
+        return bad;
+    };
+    auto span = [&](int64_t r, int64_t m) {  // m contiguous source values starting at row r
+        if (!dst) return scan_f32(static_cast<const float*>(src) + r * src_ld, m);
+        if (src_is_f64) return cast_f64(static_cast<const double*>(src) + r * src_ld, dst + r * n_cols, m);
+        return copy_f32(static_cast<const float*>(src) + r * src_ld, dst + r * n_cols, m);
+    };
+    auto work = [&](int k) {
+        const int64_t r0 = n * k / nt, r1 = n * (k + 1) / nt;
+        int bad = 0;
+        if (src_ld == n_cols) {
+            bad = span(r0, (r1 - r0) * n_cols);  // dense rows: one span
+        } else {
+            for (int64_t r = r0; r < r1; ++r) bad |= span(r, n_cols);
+        }
+        inf_seen[(size_t)k] = bad;
+    };
+    if (nt == 1)
+        work(0);
+    else
+        ccfd_parallel_for(nt, work);
+    *has_inf = 0;
+    for (int b : inf_seen) *has_inf |= b;
+    return CCFD_OK;
+}
+
 extern "C" int ccfd_cast_rows(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst,
                               int32_t* has_inf) {
     return ccfd_guarded("ccfd_cast_rows", [&]() -> int {
         if (!src || !has_inf || n < 0 || n_cols < 1 || src_ld < n_cols) return ccfd_fail(CCFD_EINVAL, "bad argument");
         if (!dst && src_is_f64) return ccfd_fail(CCFD_EINVAL, "dst may be null (scan only) for float32 input only");
-        constexpr int64_t kValuesPerPart = 1 << 19;
-        const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(ccfd_host_threads(), n * n_cols / kValuesPerPart));
-        std::vector<int> inf_seen((size_t)nt, 0);
-        // spans of contiguous values; +-inf is "exponent all ones, mantissa zero" (NaN is allowed): an integer
-        // test on the bits, which the host compiler vectorises
-        auto is_inf = [](float v) {
-            uint32_t u;
-            memcpy(&u, &v, 4);
-            return (int)((u & 0x7FFFFFFFu) == 0x7F800000u);
-        };
-        auto scan_f32 = [&](const float* sp, int64_t m) {
-            int bad = 0;
-            for (int64_t i = 0; i < m; ++i) bad |= is_inf(sp[i]);
-            return bad;
-        };
-        auto copy_f32 = [&](const float* sp, float* d, int64_t m) {
-            int bad = 0;
-            for (int64_t i = 0; i < m; ++i) {
-                d[i] = sp[i];
-                bad |= is_inf(sp[i]);
-            }
-            return bad;
-        };
-        auto cast_f64 = [&](const double* sp, float* d, int64_t m) {
-            int bad = 0;
-            for (int64_t i = 0; i < m; ++i) {
-                const float v = (float)sp[i];
-                d[i] = v;
-                bad |= is_inf(v);
-            }
-            return bad;
-        };
-        auto span = [&](int64_t r, int64_t m) {  // m contiguous source values starting at row r
-            if (!dst) return scan_f32(static_cast<const float*>(src) + r * src_ld, m);
-            if (src_is_f64) return cast_f64(static_cast<const double*>(src) + r * src_ld, dst + r * n_cols, m);
-            return copy_f32(static_cast<const float*>(src) + r * src_ld, dst + r * n_cols, m);
-        };
-        auto work = [&](int k) {
-            const int64_t r0 = n * k / nt, r1 = n * (k + 1) / nt;
-            int bad = 0;
-            if (src_ld == n_cols) {
-                bad = span(r0, (r1 - r0) * n_cols);  // dense rows: one span
-            } else {
-                for (int64_t r = r0; r < r1; ++r) bad |= span(r, n_cols);
-            }
-            inf_seen[(size_t)k] = bad;
-        };
-        if (nt == 1)
-            work(0);
-        else
-            ccfd_parallel_for(nt, work);
-        *has_inf = 0;
-        for (int b : inf_seen) *has_inf |= b;
-        return CCFD_OK;
+        return ccfd_cast_span(src, src_is_f64, n, n_cols, src_ld, dst, has_inf);
     });
 }

@@ -27,15 +27,10 @@ def _ptr(a: np.ndarray):
     return a.ctypes.data_as(ctypes.c_void_p)
 
 
-def validate_X(X, n_features: int, scratch=None) -> np.ndarray:
-    """Mirror ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625).
-
-    Any real dtype / memory order / nested list is accepted and cast to a C-ordered
-    float32 matrix; NaN is allowed (trees route it by missing_go_to_left); 1-D
-    input, zero rows, a wrong feature count and +-inf (or a float64 that overflows
-    float32) raise ValueError, as scikit-learn does.  ``scratch`` (optional, a dict the caller keeps)
-    lets repeated calls reuse one float32 buffer instead of faulting in fresh pages every request.
-    """
+def coerce_X(X, n_features: int) -> np.ndarray:
+    """Shape and type checks of ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625),
+    before any cast: a 2-D numeric array with at least one row and exactly n_features columns, or the
+    ValueError scikit-learn raises."""
     X = np.asarray(X)
     if X.dtype == object or X.dtype.kind not in "fiub":
         try:
@@ -49,9 +44,28 @@ def validate_X(X, n_features: int, scratch=None) -> np.ndarray:
         raise ValueError(f"Found array with 0 sample(s) (shape={X.shape}) while a minimum of 1 is required.")
     if X.shape[1] != n_features:
         raise ValueError(f"X has {X.shape[1]} features, but the forest is expecting {n_features} features as input.")
-    if X.dtype in (np.float64, np.float32) and X.strides[1] == X.itemsize and X.strides[0] % X.itemsize == 0 \
-            and X.strides[0] >= X.shape[1] * X.itemsize and X.size >= 4096:
-        # the usual case (a C-ordered float matrix): cast and finiteness scan in one native, threaded pass
+    return X
+
+
+def _row_major_float(X: np.ndarray) -> bool:
+    """float32 / float64 rows with unit column stride and a row stride that is a whole number of elements:
+    what the native cast (ccfd_cast_rows, ccfd_predict_proba_rows) reads in place."""
+    return (X.dtype in (np.float64, np.float32) and X.strides[1] == X.itemsize and X.strides[0] % X.itemsize == 0
+            and X.strides[0] >= X.shape[1] * X.itemsize)
+
+
+def validate_X(X, n_features: int, scratch=None) -> np.ndarray:
+    """Mirror ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625).
+
+    Any real dtype / memory order / nested list is accepted and cast to a C-ordered
+    float32 matrix; NaN is allowed (trees route it by missing_go_to_left); 1-D
+    input, zero rows, a wrong feature count and +-inf (or a float64 that overflows
+    float32) raise ValueError, as scikit-learn does.  ``scratch`` (optional, a dict the caller keeps)
+    lets repeated calls reuse one float32 buffer instead of faulting in fresh pages every request.
+    """
+    X = coerce_X(X, n_features)
+    if _row_major_float(X) and X.size >= 4096:
+        # the usual case (a C-ordered float matrix): cast and finiteness scan in one native pass
         dense32 = X.dtype == np.float32 and X.flags.c_contiguous
         if dense32:
             X32 = X  # dense float32 rows are used in place
@@ -132,6 +146,19 @@ class Forest:
         if out is None:
             out = np.empty((n, 2), dtype=np.float64)
         _lib.check(_lib.lib().ccfd_predict_proba(self.handle, _ptr(X32), n, ld, _ptr(out), _lib.KERNELS[kernel], None))
+        return out
+
+    def predict_rows(self, X: np.ndarray, kernel: str = "auto", out: np.ndarray | None = None) -> np.ndarray:
+        """A float64 / float32 request matrix in ordinary host memory -> (n, 2) float64, validation
+        included: cast, infinity check and scoring pipelined in the library (ccfd_predict_proba_rows).
+        Raises ValueError for +-inf / float32 overflow, as scikit-learn does."""
+        if not _row_major_float(X):
+            raise ValueError("predict_rows needs float32 / float64 rows with unit column stride")
+        n = X.shape[0]
+        if out is None:
+            out = np.empty((n, 2), dtype=np.float64)
+        _lib.check(_lib.lib().ccfd_predict_proba_rows(self.handle, _ptr(X), int(X.dtype == np.float64), n,
+                                                      X.strides[0] // X.itemsize, _ptr(out), _lib.KERNELS[kernel], None))
         return out
 
     def decide(self, X32: np.ndarray, threshold: float = 0.5, ge: bool = False, want_proba: bool = False,
@@ -319,10 +346,13 @@ class CcfdForestModel:
         tl = self._tls
         if not hasattr(tl, "scratch"):
             tl.scratch = {}
-        X32 = validate_X(X, self.n_features_in_, tl.scratch)
-        n = X32.shape[0]
+        Xa = coerce_X(X, self.n_features_in_)
+        n = Xa.shape[0]
+        small = self._session is not None and n <= self._session.max_batch
+        fused = not small and not (self._multi is not None and n >= 65536) and _row_major_float(Xa)
+        X32 = None if fused else validate_X(Xa, self.n_features_in_, tl.scratch)
         t1 = time.perf_counter()
-        if self._session is not None and n <= self._session.max_batch:
+        if small:
             slot = self._free_slots.get()  # blocks only when every slot is in flight
             with self._stat_lock:
                 self._in_flight += 1
@@ -334,14 +364,20 @@ class CcfdForestModel:
                     self._in_flight -= 1
                 self._free_slots.put(slot)
             path = "session"
-        elif self._multi is not None and n >= 65536:
+        elif X32 is not None and self._multi is not None and n >= 65536:
             P = self._multi.predict_proba(X32)
             path = "multi_gpu"
+        elif fused:
+            # bulk request straight from the wrapper's (pageable, float64 or float32) matrix: the cast, the
+            # infinity check, the copies and the scoring are one pipelined native call
+            P = self.forest.predict_rows(Xa)
+            path = "bulk"
         else:
             P = self.forest.predict_proba(X32)
             path = "bulk"
         t2 = time.perf_counter()
-        self._last = (X32[-1].copy(), P[-1].copy())  # the pair is built first, then published in one store
+        last_row = (Xa[-1] if X32 is None else X32[-1]).astype(np.float32)
+        self._last = (last_row, P[-1].copy())  # the pair is built first, then published in one store
         reg = self.metrics_registry
         reg.inc("ccfd_requests_total", 1, path=path)
         reg.inc("ccfd_rows_total", n, path=path)

@@ -121,6 +121,17 @@ CCFD_API int ccfd_forest_get_info(const ccfd_forest* forest, ccfd_forest_info* i
 CCFD_API int ccfd_predict_proba(ccfd_forest* forest, const float* X, int64_t n, int64_t ld, double* out,
                        uint32_t flags, void* stream);
 
+/* The request matrix as the Seldon wrapper hands it to predict(): n rows of n_features values in ordinary
+ * (pageable) host memory, float64 (x_is_f64 != 0; what JSON decoding produces) or float32, row stride `ld`
+ * ELEMENTS.  One call does what ForestClassifier._validate_X_predict (SK/ensemble/_forest.py:606-625: cast
+ * to float32, reject +-inf and float32 overflow, allow NaN) and predict_proba (:921-967) do, pipelined:
+ * the library's host threads narrow chunk k+1 into pinned memory while the GPU copies in, scores and copies
+ * out chunk k.  Input holding +-inf: CCFD_EINVAL with scikit-learn's message, *has_inf = 1 (may be NULL),
+ * `out` then partly written.  `flags`: a CCFD_KERNEL_* selector only.  Calls on one forest serialise.
+ * (ccfd_predict_proba with host pointers takes the same pipeline by itself when X is pageable float32.) */
+CCFD_API int ccfd_predict_proba_rows(ccfd_forest* forest, const void* X, int32_t x_is_f64, int64_t n, int64_t ld,
+                                     double* out, uint32_t flags, int32_t* has_inf);
+
 /* Which kernel CCFD_KERNEL_AUTO resolves to for a batch of n rows (*kernel = CCFD_KERNEL_STREAM, _SPLIT or
  * _GLOBAL) and whether a device-pointer call of that size orders its rows first (*rows_presorted, may be
  * NULL; see csrc/sort.cu).  For reports and tests; no counterpart in scikit-learn, which has one code path. */

@@ -222,6 +222,37 @@ def test_seldon_model_class_contract(ccfd):
     m.close()
 
 
+def test_bulk_requests_from_pageable_float64_and_float32_matrices(ccfd):
+    """What the Seldon wrapper hands predict() for a bulk request: an ordinary numpy matrix, float64 after
+    JSON decoding.  Cast, infinity check, copies and scoring are one pipelined native call
+    (ccfd_predict_proba_rows); plain ccfd_predict_proba takes the same pipeline for pageable float32."""
+    _, model = ccfd
+    raw, X, P, _ = load_golden("small_hard")
+    reps = 150  # 225,000 rows: four pipeline chunks, the last one ragged
+    big, want = np.tile(np.ascontiguousarray(X, dtype=np.float32), (reps, 1)), np.tile(P, (reps, 1))
+    m = model.CcfdForestModel(_fa(raw), session_max_batch=256)
+    assert np.array_equal(bits(m.predict(big.astype(np.float64))), bits(want))
+    assert np.array_equal(bits(m.predict(big)), bits(want))
+    wide = np.zeros((len(big), 41), dtype=np.float64)
+    wide[:, :30] = big
+    assert np.array_equal(bits(m.predict(wide[:, :30])), bits(want))          # strided rows, read in place
+    assert np.array_equal(bits(m.predict(np.asfortranarray(big[:70_000]))), bits(want[:70_000]))  # not row-major: numpy cast path
+    assert np.array_equal(bits(m.forest.predict_proba(big)), bits(want))       # pageable float32 through ccfd_predict_proba
+    assert np.array_equal(bits(m.forest.predict_rows(big[:9000].astype(np.float64), kernel="global")), bits(want[:9000]))
+    for pos, val in ((3, np.inf), (150_000, -np.inf), (224_999, 1e39)):
+        bad = big.astype(np.float64)
+        bad[pos, 7] = val
+        with pytest.raises(ValueError, match="infinity"):
+            m.predict(bad)
+    nan = big[:80_000].astype(np.float64)
+    nan[::5, 2] = np.nan  # NaN is allowed
+    from oracle import rf_oracle
+    assert np.array_equal(bits(m.predict(nan)), bits(rf_oracle.predict_proba_c(raw, nan.astype(np.float32))))
+    x_last, p_last = m._last
+    assert x_last.dtype == np.float32 and p_last.shape == (2,)
+    m.close()
+
+
 def test_session_slots_and_buckets(ccfd):
     _, model = ccfd
     raw, X, P, _ = load_golden("small_hard")
