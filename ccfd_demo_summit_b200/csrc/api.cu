@@ -1,5 +1,8 @@
 // Scoring entry points and the latency session (host code above the kernels).
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -54,7 +57,10 @@ int enqueue_device(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel, cu
     return rc;
 }
 
-constexpr int64_t kPageableChunkRows = 65536;  // 7.5 MB of fp32 rows per pipeline step
+// Rows per pipeline step of the pageable-host path.  Measured on the B200 box with the 284,807-row batch:
+// steps of 65,536 rows cost 0.23 ms of enqueueing each (copy-in, launch, copy-out) and 4.0-4.4 ms in all,
+// one step for the whole batch 2.5 ms: the steps only pay once a request is far beyond a million rows.
+constexpr int64_t kPageableChunkRows = 1 << 20;
 
 int ensure_pinned(ccfd_forest* f, int64_t rows) {
     if (f->pin_rows >= rows) return CCFD_OK;
@@ -101,40 +107,85 @@ int score_pageable(ccfd_forest* f, const void* X, int32_t is_f64, int64_t n, int
         if (!fl[s].live) return CCFD_OK;
         fl[s].live = false;
         CCFD_CUDA(cudaStreamSynchronize(f->stage_stream[s]));
-        if (out) memcpy(out + 2 * fl[s].r0, f->pin_p[s], sizeof(double) * 2 * (size_t)fl[s].rows);
-        if (decision) memcpy(decision + fl[s].r0, f->pin_d[s], (size_t)fl[s].rows);
+        // the caller's result array is usually fresh memory: every page faults on first touch, so the
+        // copy is spread over the host pool (4.5 MB of results: 1.5 ms on one thread, a fifth of that on the pool)
+        auto spread = [](void* dst, const void* src, size_t bytes) {
+            constexpr size_t kPart = 256 * 1024;
+            const int parts = (int)std::min<size_t>((bytes + kPart - 1) / kPart, (size_t)ccfd_host_threads());
+            if (parts <= 1) {
+                memcpy(dst, src, bytes);
+                return;
+            }
+            ccfd_parallel_for(parts, [&](int k) {
+                const size_t lo = bytes * (size_t)k / (size_t)parts / 64 * 64, hi = k + 1 == parts ? bytes : bytes * (size_t)(k + 1) / (size_t)parts / 64 * 64;
+                memcpy(static_cast<char*>(dst) + lo, static_cast<const char*>(src) + lo, hi - lo);
+            });
+        };
+        if (out) spread(out + 2 * fl[s].r0, f->pin_p[s], sizeof(double) * 2 * (size_t)fl[s].rows);
+        if (decision) spread(decision + fl[s].r0, f->pin_d[s], (size_t)fl[s].rows);
         return CCFD_OK;
     };
+    const bool trace = getenv("CCFD_TRACE_PAGEABLE") != nullptr;  // development aid: where a call's time goes
+    double t_finish = 0, t_cast = 0, t_enq = 0;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_begin = now();
     int k = 0;
     for (int64_t r0 = 0; r0 < n && rc == CCFD_OK; r0 += chunk, ++k) {
         const int s = k & 1;
         const int64_t rows = std::min<int64_t>(chunk, n - r0);
+        double t0 = now();
         rc = finish(s);  // chunk k-2 used this slot
+        t_finish += now() - t0;
         if (rc != CCFD_OK) break;
         int32_t bad = 0;
+        t0 = now();
         const void* src = is_f64 ? static_cast<const void*>(static_cast<const double*>(X) + r0 * ld)
                                  : static_cast<const void*>(static_cast<const float*>(X) + r0 * ld);
-        rc = ccfd_cast_span(src, is_f64, rows, F, ld, f->pin_x[s], &bad);
+        rc = ccfd_cast_span(src, is_f64, rows, F, ld, f->pin_x[s], &bad, 65536, getenv("CCFD_NO_STREAM_STORES") == nullptr);  // every pool thread takes part
         if (rc != CCFD_OK) break;
+        t_cast += now() - t0;
         if (bad && has_inf) {
             *has_inf = 1;
             break;
         }
+        t0 = now();
         cudaStream_t st = f->stage_stream[s];
+        cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+        if (trace) {
+            for (auto& e : ev) cudaEventCreate(&e);
+            cudaEventRecord(ev[0], st);
+        }
         CCFD_CUDA(cudaMemcpyAsync(f->stage_x[s], f->pin_x[s], sizeof(float) * (size_t)rows * F, cudaMemcpyHostToDevice, st));
+        if (trace) cudaEventRecord(ev[1], st);
         ScoreArgs a{f->stage_x[s], rows, F, out ? f->stage_p[s] : nullptr, decision ? f->stage_d[s] : nullptr, threshold, ge};
         rc = enqueue_device(f, a, kernel, st);
         if (rc != CCFD_OK) break;
+        if (trace) cudaEventRecord(ev[2], st);
         if (out) CCFD_CUDA(cudaMemcpyAsync(f->pin_p[s], f->stage_p[s], sizeof(double) * 2 * (size_t)rows, cudaMemcpyDeviceToHost, st));
+        if (trace) {
+            cudaEventRecord(ev[3], st);
+            cudaEventSynchronize(ev[3]);
+            float a01 = 0, a12 = 0, a23 = 0;
+            cudaEventElapsedTime(&a01, ev[0], ev[1]);
+            cudaEventElapsedTime(&a12, ev[1], ev[2]);
+            cudaEventElapsedTime(&a23, ev[2], ev[3]);
+            fprintf(stderr, "[ccfd pageable] step %d: h2d %.3f ms, kernel %.3f ms, d2h %.3f ms\n", k, a01, a12, a23);
+            for (auto& e : ev) cudaEventDestroy(e);
+        }
         if (decision) CCFD_CUDA(cudaMemcpyAsync(f->pin_d[s], f->stage_d[s], (size_t)rows, cudaMemcpyDeviceToHost, st));
         fl[s].r0 = r0;
         fl[s].rows = rows;
         fl[s].live = true;
+        t_enq += now() - t0;
     }
+    const double t_tail = now();
     for (int j = 0; j < 2; ++j) {  // oldest first
         const int rc2 = finish((k + j) & 1);
         if (rc == CCFD_OK) rc = rc2;
     }
+    if (trace)
+        fprintf(stderr, "[ccfd pageable] %lld rows, %d chunks: total %.3f ms = cast %.3f + enqueue %.3f + waits %.3f + tail %.3f\n", (long long)n, k,
+                now() - t_begin, t_cast, t_enq, t_finish, now() - t_tail);
     return rc;
 }
 

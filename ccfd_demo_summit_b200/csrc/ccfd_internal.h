@@ -208,7 +208,10 @@ int ccfd_guarded(const char* where, F&& body) noexcept {
 void ccfd_parallel_for(int n_parts, const std::function<void(int)>& fn);
 int ccfd_host_threads();  // parts worth asking for (pool size + the caller), >= 1
 // float64 / float32 rows -> dense float32 rows (dst == null: scan only) + "holds +-inf" (ccfd_cast_rows' body)
-int ccfd_cast_span(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst, int32_t* has_inf);
+// values_per_part: how finely the work is cut for the host pool (one part = the calling thread only)
+// streaming_stores: dst is read next by a DMA engine, not by the CPU (non-temporal stores, x86)
+int ccfd_cast_span(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst, int32_t* has_inf,
+                   int64_t values_per_part, bool streaming_stores);
 
 // Is `dev`'s primary context alive in this process?  (true when the driver cannot be asked)
 bool ccfd_primary_ctx_active(int dev);

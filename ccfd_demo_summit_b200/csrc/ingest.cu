@@ -461,9 +461,43 @@ extern "C" int ccfd_format_proba(const double* p, int64_t n_rows, char* dst, int
 // Requests below ~1 M values (every latency-path request) are done on the calling thread: waking other
 // threads costs more than the pass; larger ones go to the persistent host pool (no thread is created
 // per call).
-int ccfd_cast_span(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst, int32_t* has_inf) {
-    constexpr int64_t kValuesPerPart = 1 << 19;
-    const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(ccfd_host_threads(), n * n_cols / kValuesPerPart));
+#if defined(__SSE2__)
+#include <emmintrin.h>
+namespace {
+// Streaming (non-temporal) variants for destinations a DMA engine reads next (the pinned staging of the
+// pageable-host path): ordinary stores leave the lines dirty in the CPU caches and the copy engine then pulls
+// them out of there at a quarter of its speed (measured on the B200 box: 34 MB host->device in 2.5 ms after
+// ordinary stores).  dst must be 16-byte aligned and m a multiple of 4; the tail is the caller's.
+inline int stream_copy_f32(const float* sp, float* d, int64_t m) {
+    const __m128i absmask = _mm_set1_epi32(0x7FFFFFFF), infbits = _mm_set1_epi32(0x7F800000);
+    __m128i bad = _mm_setzero_si128();
+    for (int64_t i = 0; i < m; i += 4) {
+        const __m128 v = _mm_loadu_ps(sp + i);
+        bad = _mm_or_si128(bad, _mm_cmpeq_epi32(_mm_and_si128(_mm_castps_si128(v), absmask), infbits));
+        _mm_stream_ps(d + i, v);
+    }
+    return _mm_movemask_epi8(bad) != 0;
+}
+inline int stream_cast_f64(const double* sp, float* d, int64_t m) {
+    const __m128i absmask = _mm_set1_epi32(0x7FFFFFFF), infbits = _mm_set1_epi32(0x7F800000);
+    __m128i bad = _mm_setzero_si128();
+    for (int64_t i = 0; i < m; i += 4) {
+        const __m128 lo = _mm_cvtpd_ps(_mm_loadu_pd(sp + i)), hi = _mm_cvtpd_ps(_mm_loadu_pd(sp + i + 2));  // round to nearest even
+        const __m128 v = _mm_movelh_ps(lo, hi);
+        bad = _mm_or_si128(bad, _mm_cmpeq_epi32(_mm_and_si128(_mm_castps_si128(v), absmask), infbits));
+        _mm_stream_ps(d + i, v);
+    }
+    return _mm_movemask_epi8(bad) != 0;
+}
+}  // namespace
+#define CCFD_HAVE_STREAM_STORES 1
+#else
+#define CCFD_HAVE_STREAM_STORES 0
+#endif
+
+int ccfd_cast_span(const void* src, int32_t src_is_f64, int64_t n, int64_t n_cols, int64_t src_ld, float* dst, int32_t* has_inf,
+                   int64_t values_per_part, bool streaming_stores) {
+    const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(ccfd_host_threads(), n * n_cols / std::max<int64_t>(values_per_part, 1)));
     std::vector<int> inf_seen((size_t)nt, 0);
     // spans of contiguous values; +-inf is "exponent all ones, mantissa zero" (NaN is allowed): an integer
     // test on the bits, which the host compiler vectorises
@@ -494,10 +528,29 @@ int ccfd_cast_span(const void* src, int32_t src_is_f64, int64_t n, int64_t n_col
         }
         return bad;
     };
+    const bool stream = CCFD_HAVE_STREAM_STORES && streaming_stores && dst && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
     auto span = [&](int64_t r, int64_t m) {  // m contiguous source values starting at row r
         if (!dst) return scan_f32(static_cast<const float*>(src) + r * src_ld, m);
-        if (src_is_f64) return cast_f64(static_cast<const double*>(src) + r * src_ld, dst + r * n_cols, m);
-        return copy_f32(static_cast<const float*>(src) + r * src_ld, dst + r * n_cols, m);
+        float* d = dst + r * n_cols;
+#if CCFD_HAVE_STREAM_STORES
+        if (stream) {
+            // head up to a 16-byte boundary of dst and tail below four values with ordinary stores
+            int64_t head = (int64_t)((16 - (reinterpret_cast<uintptr_t>(d) & 15u)) & 15u) / 4;
+            if (head > m) head = m;
+            const int64_t body = (m - head) / 4 * 4;
+            int bad = 0;
+            if (src_is_f64) {
+                const double* sp = static_cast<const double*>(src) + r * src_ld;
+                bad |= cast_f64(sp, d, head) | stream_cast_f64(sp + head, d + head, body) | cast_f64(sp + head + body, d + head + body, m - head - body);
+            } else {
+                const float* sp = static_cast<const float*>(src) + r * src_ld;
+                bad |= copy_f32(sp, d, head) | stream_copy_f32(sp + head, d + head, body) | copy_f32(sp + head + body, d + head + body, m - head - body);
+            }
+            return bad;
+        }
+#endif
+        if (src_is_f64) return cast_f64(static_cast<const double*>(src) + r * src_ld, d, m);
+        return copy_f32(static_cast<const float*>(src) + r * src_ld, d, m);
     };
     auto work = [&](int k) {
         const int64_t r0 = n * k / nt, r1 = n * (k + 1) / nt;
@@ -507,6 +560,9 @@ int ccfd_cast_span(const void* src, int32_t src_is_f64, int64_t n, int64_t n_col
         } else {
             for (int64_t r = r0; r < r1; ++r) bad |= span(r, n_cols);
         }
+#if CCFD_HAVE_STREAM_STORES
+        if (stream) _mm_sfence();  // streaming stores are globally visible before the part is reported done
+#endif
         inf_seen[(size_t)k] = bad;
     };
     if (nt == 1)
@@ -523,6 +579,7 @@ extern "C" int ccfd_cast_rows(const void* src, int32_t src_is_f64, int64_t n, in
     return ccfd_guarded("ccfd_cast_rows", [&]() -> int {
         if (!src || !has_inf || n < 0 || n_cols < 1 || src_ld < n_cols) return ccfd_fail(CCFD_EINVAL, "bad argument");
         if (!dst && src_is_f64) return ccfd_fail(CCFD_EINVAL, "dst may be null (scan only) for float32 input only");
-        return ccfd_cast_span(src, src_is_f64, n, n_cols, src_ld, dst, has_inf);
+        // a request below ~1 M values is done on the calling thread (waking the pool costs more than the pass)
+        return ccfd_cast_span(src, src_is_f64, n, n_cols, src_ld, dst, has_inf, (int64_t)1 << 19, getenv("CCFD_CAST_STREAM") != nullptr /* test hook: the DMA-staging variant */);
     });
 }

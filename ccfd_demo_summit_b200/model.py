@@ -346,11 +346,15 @@ class CcfdForestModel:
         tl = self._tls
         if not hasattr(tl, "scratch"):
             tl.scratch = {}
-        Xa = coerce_X(X, self.n_features_in_)
-        n = Xa.shape[0]
-        small = self._session is not None and n <= self._session.max_batch
-        fused = not small and not (self._multi is not None and n >= 65536) and _row_major_float(Xa)
-        X32 = None if fused else validate_X(Xa, self.n_features_in_, tl.scratch)
+        Xa = np.asarray(X)
+        small = self._session is not None and (Xa.ndim != 2 or Xa.shape[0] <= self._session.max_batch)
+        if small:  # the latency path (and every malformed input): one validation pass, nothing else
+            X32, fused = validate_X(Xa, self.n_features_in_, tl.scratch), False
+        else:
+            Xa = coerce_X(Xa, self.n_features_in_)
+            fused = not (self._multi is not None and Xa.shape[0] >= 65536) and _row_major_float(Xa)
+            X32 = None if fused else validate_X(Xa, self.n_features_in_, tl.scratch)
+        n = Xa.shape[0] if fused else X32.shape[0]
         t1 = time.perf_counter()
         if small:
             slot = self._free_slots.get()  # blocks only when every slot is in flight
@@ -376,7 +380,7 @@ class CcfdForestModel:
             P = self.forest.predict_proba(X32)
             path = "bulk"
         t2 = time.perf_counter()
-        last_row = (Xa[-1] if X32 is None else X32[-1]).astype(np.float32)
+        last_row = Xa[-1].astype(np.float32) if X32 is None else X32[-1].copy()
         self._last = (last_row, P[-1].copy())  # the pair is built first, then published in one store
         reg = self.metrics_registry
         reg.inc("ccfd_requests_total", 1, path=path)

@@ -47,3 +47,31 @@ def test_shape_errors():
             model.validate_X(bad, 30)
     with pytest.raises(ValueError):
         model.validate_X([["a"] * 30], 30)
+
+
+def test_streaming_store_cast_is_bit_identical_too(monkeypatch):
+    """The pageable-host path narrows rows into pinned staging with non-temporal stores (the copy engine
+    reads them next); the same code is reachable through ccfd_cast_rows with CCFD_CAST_STREAM set.  Odd sizes,
+    misaligned destinations, strided rows, both source types, infinity detection."""
+    import ctypes
+
+    from ccfd_demo_summit_b200 import _lib
+
+    monkeypatch.setenv("CCFD_CAST_STREAM", "1")
+    rng = np.random.default_rng(4)
+    L = _lib.lib()
+    for n, cols, ld, off in ((1, 30, 30, 0), (7, 30, 30, 1), (1001, 30, 37, 3), (20000, 30, 30, 0), (70001, 29, 29, 2), (40000, 31, 40, 1)):
+        for dt in (np.float64, np.float32):
+            src = (rng.standard_normal((n, ld)) * 10.0 ** rng.integers(-40, 39, (n, ld))).astype(dt)
+            src[rng.uniform(size=src.shape) < 0.01] = np.nan
+            with np.errstate(over="ignore", invalid="ignore"):
+                want = src[:, :cols].astype(np.float32)
+            buf = np.zeros(n * cols + 8, dtype=np.float32)
+            dst = buf[off: off + n * cols].reshape(n, cols)
+            bad = ctypes.c_int32(-1)
+            rc = L.ccfd_cast_rows(src.ctypes.data_as(ctypes.c_void_p), int(dt == np.float64), n, cols, ld,
+                                  dst.ctypes.data_as(ctypes.c_void_p), ctypes.byref(bad))
+            assert rc == 0
+            assert np.array_equal(dst.view(np.uint32), want.view(np.uint32)), (n, cols, ld, off, dt)
+            assert bool(bad.value) == bool(np.isinf(want).any())
+            assert buf[:off].sum() == 0 and buf[off + n * cols:].sum() == 0  # nothing written outside
