@@ -55,6 +55,7 @@ SYMBOLS = [
     ("ccfd_session_submit", c_int, [c_void_p, c_int32, c_int64]),
     ("ccfd_session_wait", c_int, [c_void_p, c_int32]),
     ("ccfd_session_run", c_int, [c_void_p, c_int32, c_int64]),
+    ("ccfd_session_score", c_int, [c_void_p, c_int32, c_void_p, c_int32, c_int64, c_int64, c_void_p, POINTER(c_int32)]),
     ("ccfd_batcher_create", c_int, [c_void_p, c_int64, POINTER(c_void_p)]),
     ("ccfd_batcher_destroy", c_int, [c_void_p]),
     ("ccfd_batcher_push", c_int, [c_void_p, c_void_p, c_int64, c_int64]),

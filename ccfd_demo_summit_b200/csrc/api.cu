@@ -440,6 +440,31 @@ static int ccfd_session_wait_impl(ccfd_session* ss, int32_t slot) {
     return CCFD_OK;
 }
 
+// One request, start to finish, in one foreign-function call: narrow / copy the caller's rows into the
+// slot's pinned buffer (float64 or float32, any row stride; scikit-learn's infinity check on the way;
+// streaming stores for all but tiny requests, so the copy engine finds the rows in memory, not in a cache),
+// launch the slot's graph, wait, copy the probabilities out.
+static int ccfd_session_score_impl(ccfd_session* ss, int32_t slot, const void* X, int32_t x_is_f64, int64_t n, int64_t ld, double* out,
+                                   int32_t* has_inf) {
+    if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
+    if (slot < 0 || slot >= (int32_t)ss->slots.size()) return ccfd_fail(CCFD_EINVAL, "slot %d out of range", slot);
+    if (!X || !out) return ccfd_fail(CCFD_EINVAL, "X and out must not be null");
+    if (n < 1 || n > ss->max_batch) return ccfd_fail(CCFD_EINVAL, "n must be in 1..%lld (got %lld)", (long long)ss->max_batch, (long long)n);
+    const int F = ss->f->dev.n_features;
+    if (ld < F) return ccfd_fail(CCFD_EINVAL, "row stride %lld is smaller than n_features %d", (long long)ld, F);
+    ccfd_slot& s = ss->slots[(size_t)slot];
+    if (s.busy) return ccfd_fail(CCFD_ESTATE, "slot %d is in flight: wait before submitting again", slot);
+    int32_t bad = 0;
+    int rc = ccfd_cast_span(X, x_is_f64, n, F, ld, s.hx, &bad, (int64_t)1 << 19, n * F >= 4096);
+    if (has_inf) *has_inf = bad;
+    if (rc != CCFD_OK) return rc;
+    if (bad) return ccfd_fail(CCFD_EINVAL, "Input X contains infinity or a value too large for dtype('float32').");
+    rc = ccfd_session_run(ss, slot, n);
+    if (rc != CCFD_OK) return rc;
+    memcpy(out, s.hp, sizeof(double) * 2 * (size_t)n);
+    return CCFD_OK;
+}
+
 int ccfd_session_geometry(const ccfd_session* ss, int64_t* max_batch, int32_t* n_slots, int32_t* n_features) {
     if (!ss) return ccfd_fail(CCFD_EINVAL, "null session");
     if (max_batch) *max_batch = ss->max_batch;
@@ -479,6 +504,10 @@ extern "C" int ccfd_session_submit(ccfd_session* ss, int32_t slot, int64_t n_row
 }
 extern "C" int ccfd_session_wait(ccfd_session* ss, int32_t slot) {
     return ccfd_guarded("ccfd_session_wait", [&]() -> int { return ccfd_session_wait_impl(ss, slot); });
+}
+extern "C" int ccfd_session_score(ccfd_session* ss, int32_t slot, const void* X, int32_t x_is_f64, int64_t n, int64_t ld, double* out,
+                                  int32_t* has_inf) {
+    return ccfd_guarded("ccfd_session_score", [&]() -> int { return ccfd_session_score_impl(ss, slot, X, x_is_f64, n, ld, out, has_inf); });
 }
 extern "C" int ccfd_session_run(ccfd_session* ss, int32_t slot, int64_t n_rows) {
     return ccfd_guarded("ccfd_session_run", [&]() -> int { return ccfd_session_run_impl(ss, slot, n_rows); });

@@ -16,6 +16,8 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <climits>
+#include <cstdint>
 #include <cstring>
 #include <deque>
 #include <thread>
@@ -117,16 +119,6 @@ int submit_current(ccfd_batcher* b) {
     return CCFD_OK;
 }
 
-inline bool row_has_inf(const float* r, int F) {
-    int bad = 0;
-    for (int i = 0; i < F; ++i) {
-        uint32_t u;
-        memcpy(&u, r + i, 4);
-        bad |= (int)((u & 0x7FFFFFFFu) == 0x7F800000u);
-    }
-    return bad != 0;
-}
-
 int push_impl(ccfd_batcher* b, const float* records, int64_t n, int64_t ld) {
     int64_t i = 0;
     while (i < n) {
@@ -134,13 +126,14 @@ int push_impl(ccfd_batcher* b, const float* records, int64_t n, int64_t ld) {
         if (rc != CCFD_OK) return rc;
         ccfd_batcher::Slot& sl = b->slots[(size_t)b->cur];
         const int64_t take = std::min<int64_t>(n - i, b->batch - b->fill);
-        for (int64_t r = 0; r < take; ++r) {
-            const float* src = records + (i + r) * ld;
-            // scikit-learn refuses +-inf before scoring (SK/ensemble/_forest.py:606-625); a record stream has
-            // nobody to raise to, so the record is refused here, before it reaches the slot
-            if (row_has_inf(src, b->F)) return ccfd_fail(CCFD_EINVAL, "record %lld holds +-infinity", (long long)(b->next_row + b->fill + r));
-            memcpy(sl.x + (b->fill + r) * b->F, src, sizeof(float) * (size_t)b->F);
-        }
+        // Records go into the pinned slot with streaming stores (the copy engine reads them next; out of a CPU
+        // cache it would pull them at a quarter of its speed), checked for +-inf on the way: scikit-learn refuses
+        // +-inf before scoring (SK/ensemble/_forest.py:606-625); a record stream has nobody to raise to, so the
+        // records are refused here.
+        int32_t bad = 0;
+        const int rc_copy = ccfd_cast_span(records + i * ld, 0, take, b->F, ld, sl.x + b->fill * b->F, &bad, INT64_MAX, take * b->F >= 1024);
+        if (rc_copy != CCFD_OK) return rc_copy;
+        if (bad) return ccfd_fail(CCFD_EINVAL, "a record in [%lld, %lld) holds +-infinity", (long long)(b->next_row + b->fill), (long long)(b->next_row + b->fill + take));
         b->fill += take;
         i += take;
         sl.t_last = Clock::now();  // arrival of the (so far) last record of this batch

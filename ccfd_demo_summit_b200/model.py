@@ -207,11 +207,16 @@ class Session:
         _lib.check(_lib.lib().ccfd_session_wait(self._h, slot))
 
     def score(self, slot: int, rows: np.ndarray) -> np.ndarray:
-        """Copy rows into the slot, run its graph, return a copy of the probabilities."""
+        """One request in one native call (ccfd_session_score): float64 / float32 rows are narrowed into the
+        slot's pinned buffer (ValueError on +-inf, as scikit-learn), the slot's graph runs, the probabilities
+        come back as a new array."""
+        if not _row_major_float(rows):
+            rows = np.ascontiguousarray(rows, dtype=np.float32)
         n = rows.shape[0]
-        self.x[slot][:n] = rows
-        _lib.check(_lib.lib().ccfd_session_run(self._h, slot, n))
-        return self.p[slot][:n].copy()
+        out = np.empty((n, 2), dtype=np.float64)
+        _lib.check(_lib.lib().ccfd_session_score(self._h, slot, _ptr(rows), int(rows.dtype == np.float64), n,
+                                                 rows.strides[0] // rows.itemsize, _ptr(out), None))
+        return out
 
     def close(self):
         if getattr(self, "_h", None) and _lib is not None:
@@ -348,8 +353,10 @@ class CcfdForestModel:
             tl.scratch = {}
         Xa = np.asarray(X)
         small = self._session is not None and (Xa.ndim != 2 or Xa.shape[0] <= self._session.max_batch)
-        if small:  # the latency path (and every malformed input): one validation pass, nothing else
-            X32, fused = validate_X(Xa, self.n_features_in_, tl.scratch), False
+        if small:  # the latency path (and every malformed input)
+            Xa = coerce_X(Xa, self.n_features_in_)
+            # float rows go to the slot as they are: the native call narrows them and checks for infinity
+            X32, fused = (Xa if _row_major_float(Xa) else validate_X(Xa, self.n_features_in_, tl.scratch)), False
         else:
             Xa = coerce_X(Xa, self.n_features_in_)
             fused = not (self._multi is not None and Xa.shape[0] >= 65536) and _row_major_float(Xa)
@@ -380,7 +387,7 @@ class CcfdForestModel:
             P = self.forest.predict_proba(X32)
             path = "bulk"
         t2 = time.perf_counter()
-        last_row = Xa[-1].astype(np.float32) if X32 is None else X32[-1].copy()
+        last_row = (Xa[-1] if X32 is None else X32[-1]).astype(np.float32)
         self._last = (last_row, P[-1].copy())  # the pair is built first, then published in one store
         reg = self.metrics_registry
         reg.inc("ccfd_requests_total", 1, path=path)

@@ -215,6 +215,15 @@ CCFD_API int ccfd_batcher_replay(ccfd_batcher* batcher, const float* records, in
                                  int32_t burst);
 CCFD_API int ccfd_batcher_stats(ccfd_batcher* batcher, int64_t* batches_done, int64_t* records_in);
 
+/* A whole request in one call: rows as the wrapper holds them (float64 if x_is_f64 != 0, else float32; row
+ * stride `ld` elements) are narrowed into slot `slot`'s pinned buffer with scikit-learn's infinity check
+ * (SK/ensemble/_forest.py:606-625: CCFD_EINVAL and *has_inf = 1, may be NULL), the slot's graph runs, and the
+ * n x 2 probabilities are copied to `out`.  Replaces, for requests of up to max_batch rows, the
+ * cast + predict_proba pair behind the Seldon wrapper's predict() (requests arriving at reference
+ * deploy/router.yaml:65-68).  One caller per slot at a time. */
+CCFD_API int ccfd_session_score(ccfd_session* session, int32_t slot, const void* X, int32_t x_is_f64, int64_t n, int64_t ld,
+                                double* out, int32_t* has_inf);
+
 /* Request text -> float32 rows, written straight into `dst` (typically a session slot's pinned x
  * buffer, so the bytes the GPU copies are produced in one pass).  Replaces the JSON decoding of the
  * Seldon Python wrapper in front of predict() for requests arriving at reference
