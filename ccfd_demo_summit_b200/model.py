@@ -49,9 +49,16 @@ def coerce_X(X, n_features: int) -> np.ndarray:
 
 def _row_major_float(X: np.ndarray) -> bool:
     """float32 / float64 rows with unit column stride and a row stride that is a whole number of elements:
-    what the native cast (ccfd_cast_rows, ccfd_predict_proba_rows) reads in place."""
-    return (X.dtype in (np.float64, np.float32) and X.strides[1] == X.itemsize and X.strides[0] % X.itemsize == 0
-            and X.strides[0] >= X.shape[1] * X.itemsize)
+    what the native cast (ccfd_cast_rows, ccfd_predict_proba_rows, ccfd_session_score) reads in place.
+    (numpy gives a length-1 axis an arbitrary stride, e.g. 0 for x[None, :]: a single row always qualifies.)"""
+    if X.dtype not in (np.float64, np.float32) or (X.shape[1] > 1 and X.strides[1] != X.itemsize):
+        return False
+    return X.shape[0] == 1 or (X.strides[0] % X.itemsize == 0 and X.strides[0] >= X.shape[1] * X.itemsize)
+
+
+def _ld(X: np.ndarray) -> int:
+    """Row stride in elements of a matrix that passed _row_major_float."""
+    return X.shape[1] if X.shape[0] == 1 else X.strides[0] // X.itemsize
 
 
 def validate_X(X, n_features: int, scratch=None) -> np.ndarray:
@@ -78,7 +85,7 @@ def validate_X(X, n_features: int, scratch=None) -> np.ndarray:
             X32 = np.empty(X.shape, dtype=np.float32)
         bad = ctypes.c_int32()
         _lib.check(_lib.lib().ccfd_cast_rows(_ptr(X), int(X.dtype == np.float64), X.shape[0], X.shape[1],
-                                             X.strides[0] // X.itemsize, None if dense32 else _ptr(X32), ctypes.byref(bad)))
+                                             _ld(X), None if dense32 else _ptr(X32), ctypes.byref(bad)))
         has_inf = bool(bad.value)
     else:
         with np.errstate(over="ignore"):
@@ -142,7 +149,7 @@ class Forest:
     # -- host buffers ---------------------------------------------------------------------
     def predict_proba(self, X32: np.ndarray, kernel: str = "auto", out: np.ndarray | None = None) -> np.ndarray:
         """Validated float32 rows in host memory (unit column stride) -> (n, 2) float64."""
-        n, ld = X32.shape[0], X32.strides[0] // 4
+        n, ld = X32.shape[0], _ld(X32)
         if out is None:
             out = np.empty((n, 2), dtype=np.float64)
         _lib.check(_lib.lib().ccfd_predict_proba(self.handle, _ptr(X32), n, ld, _ptr(out), _lib.KERNELS[kernel], None))
@@ -158,12 +165,12 @@ class Forest:
         if out is None:
             out = np.empty((n, 2), dtype=np.float64)
         _lib.check(_lib.lib().ccfd_predict_proba_rows(self.handle, _ptr(X), int(X.dtype == np.float64), n,
-                                                      X.strides[0] // X.itemsize, _ptr(out), _lib.KERNELS[kernel], None))
+                                                      _ld(X), _ptr(out), _lib.KERNELS[kernel], None))
         return out
 
     def decide(self, X32: np.ndarray, threshold: float = 0.5, ge: bool = False, want_proba: bool = False,
                kernel: str = "auto"):
-        n, ld = X32.shape[0], X32.strides[0] // 4
+        n, ld = X32.shape[0], _ld(X32)
         dec = np.empty(n, dtype=np.uint8)
         out = np.empty((n, 2), dtype=np.float64) if want_proba else None
         _lib.check(_lib.lib().ccfd_predict_decision(self.handle, _ptr(X32), n, ld, _ptr(out) if want_proba else None,
@@ -215,7 +222,7 @@ class Session:
         n = rows.shape[0]
         out = np.empty((n, 2), dtype=np.float64)
         _lib.check(_lib.lib().ccfd_session_score(self._h, slot, _ptr(rows), int(rows.dtype == np.float64), n,
-                                                 rows.strides[0] // rows.itemsize, _ptr(out), None))
+                                                 _ld(rows), _ptr(out), None))
         return out
 
     def close(self):

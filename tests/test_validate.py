@@ -75,3 +75,16 @@ def test_streaming_store_cast_is_bit_identical_too(monkeypatch):
             assert np.array_equal(dst.view(np.uint32), want.view(np.uint32)), (n, cols, ld, off, dt)
             assert bool(bad.value) == bool(np.isinf(want).any())
             assert buf[:off].sum() == 0 and buf[off + n * cols:].sum() == 0  # nothing written outside
+
+
+def test_single_row_views_with_arbitrary_outer_stride_are_row_major():
+    from ccfd_demo_summit_b200 import model
+
+    x = np.arange(30, dtype=np.float32)
+    for view in (x[None, :], np.broadcast_to(x, (1, 30)), x.reshape(1, 30)):
+        assert model._row_major_float(view) and model._ld(view) == 30
+        assert np.array_equal(model.validate_X(view, 30), x[None, :])
+    wide = np.zeros((5, 41))
+    assert model._row_major_float(wide[:, :30]) and model._ld(wide[:, :30]) == 41
+    assert not model._row_major_float(np.asfortranarray(np.zeros((5, 30))))
+    assert not model._row_major_float(np.zeros((5, 30), dtype=np.int64))
