@@ -47,15 +47,37 @@ class Registry:
     def declare(self, name: str, kind: str, buckets=None):
         self._meta[name] = (kind, tuple(buckets) if buckets else None)
 
+    @staticmethod
+    def key(name: str, **labels):
+        """The cell key of (name, labels): build it once, pass it to inc_key / observe_key on the hot path."""
+        return (name, tuple(sorted(labels.items())))
+
     def inc(self, name: str, value=1, **labels):
-        d = self._mine()
-        key = (name, tuple(sorted(labels.items())))
-        d[key] = d.get(key, 0) + value
+        self.inc_key(self.key(name, **labels), value)
 
     def observe(self, name: str, value: float, **labels):
-        kind, buckets = self._meta[name]
+        self.observe_key(self.key(name, **labels), value)
+
+    def cells(self) -> dict:
+        """The calling thread's cells: fetch once per request, then update with plain dictionary operations
+        (counters) and observe_in (histograms)."""
+        return self._mine()
+
+    def observe_in(self, d: dict, key, value: float):
+        buckets = self._meta[key[0]][1]
+        cell = d.get(key)
+        if cell is None:
+            cell = d[key] = [0] * (len(buckets) + 1) + [0.0]
+        cell[bisect.bisect_left(buckets, value)] += 1
+        cell[-1] += value
+
+    def inc_key(self, key, value=1):
         d = self._mine()
-        key = (name, tuple(sorted(labels.items())))
+        d[key] = d.get(key, 0) + value
+
+    def observe_key(self, key, value: float):
+        buckets = self._meta[key[0]][1]
+        d = self._mine()
         cell = d.get(key)
         if cell is None:
             cell = d[key] = [0] * (len(buckets) + 1) + [0.0]  # per-bucket counts (+Inf last), then the sum

@@ -350,6 +350,9 @@ class CcfdForestModel:
         reg.declare("ccfd_request_rows", "histogram", metrics.BATCH_BUCKETS)
         reg.declare("ccfd_score_seconds", "histogram", metrics.LATENCY_BUCKETS)
         reg.declare("ccfd_predict_seconds", "histogram", metrics.LATENCY_BUCKETS)
+        self._metric_keys = {p: (reg.key("ccfd_requests_total", path=p), reg.key("ccfd_rows_total", path=p), reg.key("ccfd_request_rows"),
+                                 reg.key("ccfd_score_seconds", path=p), reg.key("ccfd_predict_seconds", path=p))
+                             for p in ("session", "bulk", "multi_gpu")}
 
     def predict(self, X, feature_names=None, meta=None):
         """The Seldon wrapper passes the names positionally; like scikit-learn on a forest fitted
@@ -396,12 +399,13 @@ class CcfdForestModel:
         t2 = time.perf_counter()
         last_row = (Xa[-1] if X32 is None else X32[-1]).astype(np.float32)
         self._last = (last_row, P[-1].copy())  # the pair is built first, then published in one store
-        reg = self.metrics_registry
-        reg.inc("ccfd_requests_total", 1, path=path)
-        reg.inc("ccfd_rows_total", n, path=path)
-        reg.observe("ccfd_request_rows", n)
-        reg.observe("ccfd_score_seconds", t2 - t1, path=path)   # copy-in + kernels + result visible on the host
-        reg.observe("ccfd_predict_seconds", t2 - t0, path=path)  # with validation / cast
+        reg, k = self.metrics_registry, self._metric_keys[path]  # keys built once; this thread's cells fetched once
+        d = reg.cells()
+        d[k[0]] = d.get(k[0], 0) + 1
+        d[k[1]] = d.get(k[1], 0) + n
+        reg.observe_in(d, k[2], n)
+        reg.observe_in(d, k[3], t2 - t1)  # copy-in + kernels + result visible on the host
+        reg.observe_in(d, k[4], t2 - t0)  # with validation / cast
         return P
 
     def decide(self, X, threshold: float | None = None, ge: bool = False):
