@@ -41,6 +41,7 @@ constexpr int kTileThreads = 256;                      // SPLIT: one row per thr
 // CTAs 8.97 ms, 512: 11.1, 768: 8.02, 1024: 8.11).  Batches too small to give every SM such a CTA use
 // 256-row CTAs.
 constexpr int kGlobalThreadsBulk = 768;
+constexpr int kGlobalThreadsBulkAlt = 1024;  // CCFD_GLOBAL_THREADS=1024 (tuning knob)
 constexpr int kGlobalThreadsSmall = 256;
 constexpr int kGlobalThreadsWide = 64;  // rows with so many features that 256 of them overflow shared memory
 constexpr int kSplitStages = 2;
@@ -952,6 +953,7 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));   \
     CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
         CCFD_GLOBAL_ATTRS(1, kGlobalThreadsBulk)
+        CCFD_GLOBAL_ATTRS(2, kGlobalThreadsBulkAlt)
         CCFD_GLOBAL_ATTRS(4, kGlobalThreadsBulk)
         CCFD_GLOBAL_ATTRS(4, kGlobalThreadsSmall)
         CCFD_GLOBAL_ATTRS(4, kGlobalThreadsWide)
@@ -1166,6 +1168,11 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
     } else if (kernel == CCFD_KERNEL_GLOBAL) {
         auto xs_bytes = [&](int threads) { return round_up((uint32_t)(f->dev.n_features + 1) * (uint32_t)threads * 4u, 128u); };
         int threads = a.n >= (int64_t)f->sm_count * kGlobalThreadsBulk ? kGlobalThreadsBulk : kGlobalThreadsSmall;
+        if (threads == kGlobalThreadsBulk) {
+            if (const char* e = getenv("CCFD_GLOBAL_THREADS")) {  // tuning knob
+                if (atoi(e) == kGlobalThreadsBulkAlt && xs_bytes(kGlobalThreadsBulkAlt) <= (uint32_t)f->smem_optin) threads = kGlobalThreadsBulkAlt;
+            }
+        }
         if (threads == kGlobalThreadsBulk && xs_bytes(threads) > (uint32_t)f->smem_optin) threads = kGlobalThreadsSmall;
         if (threads == kGlobalThreadsSmall && xs_bytes(threads) > (uint32_t)f->smem_optin) threads = kGlobalThreadsWide;
         const int64_t tiles = (a.n + threads - 1) / threads;
@@ -1182,7 +1189,10 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         else if (wide) k_global<1, TH_, true><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);              \
         else k_global<1, TH_, false><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);                       \
     } while (0)
-        if (threads == kGlobalThreadsBulk) CCFD_LAUNCH_GLOBAL(kGlobalThreadsBulk);
+        if (threads == kGlobalThreadsBulkAlt) {
+            if (wide) k_global<2, kGlobalThreadsBulkAlt, true><<<(unsigned)tiles, kGlobalThreadsBulkAlt, gsmem, stream>>>(f->dev, a, vec_ok);
+            else k_global<2, kGlobalThreadsBulkAlt, false><<<(unsigned)tiles, kGlobalThreadsBulkAlt, gsmem, stream>>>(f->dev, a, vec_ok);
+        } else if (threads == kGlobalThreadsBulk) CCFD_LAUNCH_GLOBAL(kGlobalThreadsBulk);
         else if (threads == kGlobalThreadsSmall) CCFD_LAUNCH_GLOBAL(kGlobalThreadsSmall);
         else CCFD_LAUNCH_GLOBAL(kGlobalThreadsWide);
 #undef CCFD_LAUNCH_GLOBAL

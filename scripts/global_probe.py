@@ -20,12 +20,13 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--trees", type=int, default=500)
     ap.add_argument("--rows", type=int, default=10_000_000)
-    ap.add_argument("--variants", default="sort=1;sort=0;sort=1,nt=4;sort=1,nt=1;sort=0,nt=4")
+    ap.add_argument("--variants", default="sort=1;sort=0;sort=1,carve=60;sort=1,carve=85;sort=1,carve=100;sort=1,threads=1024,carve=60;sort=1,threads=1024,carve=75")
     args = ap.parse_args()
     X, y = synth.make_dataset(seed=1, labels="hard")
     t0 = time.time()
     rf = synth.fit_forest(X, y, n_estimators=args.trees, max_depth=None)
-    forest = model.Forest(converter.from_sklearn(rf))
+    fa = converter.from_sklearn(rf)
+    forest = model.Forest(fa)
     print(json.dumps({"fit_s": round(time.time() - t0, 1), **forest.info}), flush=True)
     n = args.rows
     xs = device_rows(X, n)
@@ -33,12 +34,25 @@ def main():
     for var in args.variants.split(";"):
         kv = dict(p.split("=") for p in var.split(","))
         os.environ["CCFD_ROW_SORT"] = kv.get("sort", "1")
+        for name, env in (("threads", "CCFD_GLOBAL_THREADS"),):
+            if name in kv:
+                os.environ[env] = kv[name]
+            else:
+                os.environ.pop(env, None)
+        if "carve" in kv:  # the carve-out is set when a forest is bound to the device: a forest of its own
+            os.environ["CCFD_GLOBAL_CARVEOUT"] = kv["carve"]
+            forest_v = model.Forest(fa)
+        else:
+            os.environ.pop("CCFD_GLOBAL_CARVEOUT", None)
+            forest_v = forest
         if "nt" in kv:
             os.environ["CCFD_GLOBAL_NT"] = kv["nt"]
         else:
             os.environ.pop("CCFD_GLOBAL_NT", None)
         out = torch.empty((n, 2), dtype=torch.float64, device="cuda")
-        ms = time_device(forest, xs, n, out, "global", iters=3, warm=1)
+        ms = time_device(forest_v, xs, n, out, "global", iters=3, warm=1)
+        if forest_v is not forest:
+            forest_v.close()
         same = True if ref is None else bool(torch.equal(out.view(torch.int64), ref.view(torch.int64)))
         if ref is None:
             ref = out
