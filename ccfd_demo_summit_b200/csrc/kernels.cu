@@ -41,7 +41,6 @@ constexpr int kTileThreads = 256;                      // SPLIT: one row per thr
 // CTAs 8.97 ms, 512: 11.1, 768: 8.02, 1024: 8.11).  Batches too small to give every SM such a CTA use
 // 256-row CTAs.
 constexpr int kGlobalThreadsBulk = 768;
-constexpr int kGlobalThreadsBulkAlt = 1024;  // CCFD_GLOBAL_THREADS=1024 (tuning knob)
 constexpr int kGlobalThreadsSmall = 256;
 constexpr int kGlobalThreadsWide = 64;  // rows with so many features that 256 of them overflow shared memory
 constexpr int kSplitStages = 2;
@@ -660,8 +659,14 @@ __device__ __forceinline__ void descend_global(const GlobalTree (&gt)[NT], const
 // kGlobalTrees trees per thread at a time: two independent chains of dependent loads per thread.
 // (Measured on unbounded-depth forests with the L1 carve-out below: 1 tree 12.1 ms, 2 trees 9.1 ms,
 // 4 trees 10.8 ms per 2 M rows x 100 trees.)
-template <int kGlobalTrees, int kGlobalThreads, bool WIDE>
-__global__ void __launch_bounds__(kGlobalThreads) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
+// TWO_PER_SM (pre-sorted bulk launches): with the rows in key order a warp-wide node load touches ~5 sectors
+// instead of ~20 and the kernel is bound by the latency of its dependent loads, not by L1 any more
+// (profiles/r2_k_global_ncu_summary.txt: long_scoreboard 5.8 stall cycles per issued instruction), so it
+// pays to give most of the SM to shared memory (85 % carve-out), hold TWO 768-row CTAs and double the
+// chains in flight: 500 unbounded trees x 10 M rows 133.7 -> 101.5 ms.  For rows in arrival order the same
+// setting is far worse (237 -> 368 ms: L1 is what keeps that case alive), hence a kernel of its own.
+template <int kGlobalTrees, int kGlobalThreads, bool WIDE, bool TWO_PER_SM = false>
+__global__ void __launch_bounds__(kGlobalThreads, TWO_PER_SM ? 2 : 1) k_global(const ForestDev f, const ScoreArgs a, const int vec_ok) {
     constexpr int S = kGlobalThreads, XS = S;
     extern __shared__ __align__(128) uint8_t smem[];
     float* xs = reinterpret_cast<float*>(smem);
@@ -953,7 +958,6 @@ int ccfd_kernels_init(ccfd_forest* f) {
     CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));   \
     CCFD_CUDA(cudaFuncSetAttribute(k_global<NT_, TH_, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout));
         CCFD_GLOBAL_ATTRS(1, kGlobalThreadsBulk)
-        CCFD_GLOBAL_ATTRS(2, kGlobalThreadsBulkAlt)
         CCFD_GLOBAL_ATTRS(4, kGlobalThreadsBulk)
         CCFD_GLOBAL_ATTRS(4, kGlobalThreadsSmall)
         CCFD_GLOBAL_ATTRS(4, kGlobalThreadsWide)
@@ -963,6 +967,12 @@ int ccfd_kernels_init(ccfd_forest* f) {
         CCFD_GLOBAL_ATTRS(1, kGlobalThreadsWide)
         CCFD_GLOBAL_ATTRS(2, kGlobalThreadsWide)
 #undef CCFD_GLOBAL_ATTRS
+        int carveout_sorted = 85;
+        if (const char* e = getenv("CCFD_GLOBAL_CARVEOUT_SORTED")) carveout_sorted = atoi(e);  // tuning knob
+        CCFD_CUDA(cudaFuncSetAttribute(k_global<2, kGlobalThreadsBulk, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+        CCFD_CUDA(cudaFuncSetAttribute(k_global<2, kGlobalThreadsBulk, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout_sorted));
+        CCFD_CUDA(cudaFuncSetAttribute(k_global<2, kGlobalThreadsBulk, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->smem_optin));
+        CCFD_CUDA(cudaFuncSetAttribute(k_global<2, kGlobalThreadsBulk, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout_sorted));
     }
 
     // STREAM ring geometry: a stage holds the largest tree and at least 128 rows of features.
@@ -1168,11 +1178,6 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
     } else if (kernel == CCFD_KERNEL_GLOBAL) {
         auto xs_bytes = [&](int threads) { return round_up((uint32_t)(f->dev.n_features + 1) * (uint32_t)threads * 4u, 128u); };
         int threads = a.n >= (int64_t)f->sm_count * kGlobalThreadsBulk ? kGlobalThreadsBulk : kGlobalThreadsSmall;
-        if (threads == kGlobalThreadsBulk) {
-            if (const char* e = getenv("CCFD_GLOBAL_THREADS")) {  // tuning knob
-                if (atoi(e) == kGlobalThreadsBulkAlt && xs_bytes(kGlobalThreadsBulkAlt) <= (uint32_t)f->smem_optin) threads = kGlobalThreadsBulkAlt;
-            }
-        }
         if (threads == kGlobalThreadsBulk && xs_bytes(threads) > (uint32_t)f->smem_optin) threads = kGlobalThreadsSmall;
         if (threads == kGlobalThreadsSmall && xs_bytes(threads) > (uint32_t)f->smem_optin) threads = kGlobalThreadsWide;
         const int64_t tiles = (a.n + threads - 1) / threads;
@@ -1189,9 +1194,11 @@ int ccfd_launch_score(const ccfd_forest* f, const ScoreArgs& a, uint32_t kernel,
         else if (wide) k_global<1, TH_, true><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);              \
         else k_global<1, TH_, false><<<(unsigned)tiles, TH_, gsmem, stream>>>(f->dev, a, vec_ok);                       \
     } while (0)
-        if (threads == kGlobalThreadsBulkAlt) {
-            if (wide) k_global<2, kGlobalThreadsBulkAlt, true><<<(unsigned)tiles, kGlobalThreadsBulkAlt, gsmem, stream>>>(f->dev, a, vec_ok);
-            else k_global<2, kGlobalThreadsBulkAlt, false><<<(unsigned)tiles, kGlobalThreadsBulkAlt, gsmem, stream>>>(f->dev, a, vec_ok);
+        const bool one_per_sm = getenv("CCFD_GLOBAL_ONE_PER_SM") != nullptr;  // tuning knob (read per launch): sorted launches as before
+        if (a.perm && threads == kGlobalThreadsBulk && nt == 2 && !one_per_sm && 2 * gsmem + 4096 <= (uint32_t)f->smem_optin) {
+            // pre-sorted bulk launch: two CTAs per SM (see k_global's comment)
+            if (wide) k_global<2, kGlobalThreadsBulk, true, true><<<(unsigned)tiles, kGlobalThreadsBulk, gsmem, stream>>>(f->dev, a, vec_ok);
+            else k_global<2, kGlobalThreadsBulk, false, true><<<(unsigned)tiles, kGlobalThreadsBulk, gsmem, stream>>>(f->dev, a, vec_ok);
         } else if (threads == kGlobalThreadsBulk) CCFD_LAUNCH_GLOBAL(kGlobalThreadsBulk);
         else if (threads == kGlobalThreadsSmall) CCFD_LAUNCH_GLOBAL(kGlobalThreadsSmall);
         else CCFD_LAUNCH_GLOBAL(kGlobalThreadsWide);

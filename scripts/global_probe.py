@@ -20,7 +20,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--trees", type=int, default=500)
     ap.add_argument("--rows", type=int, default=10_000_000)
-    ap.add_argument("--variants", default="sort=1;sort=0;sort=1,carve=60;sort=1,carve=85;sort=1,carve=100;sort=1,threads=1024,carve=60;sort=1,threads=1024,carve=75")
+    ap.add_argument("--variants", default="sort=1;sort=0;sort=1,one=1;sort=1,carves=100;sort=1,carves=70")
     args = ap.parse_args()
     X, y = synth.make_dataset(seed=1, labels="hard")
     t0 = time.time()
@@ -34,16 +34,16 @@ def main():
     for var in args.variants.split(";"):
         kv = dict(p.split("=") for p in var.split(","))
         os.environ["CCFD_ROW_SORT"] = kv.get("sort", "1")
-        for name, env in (("threads", "CCFD_GLOBAL_THREADS"),):
+        for name, env in (("one", "CCFD_GLOBAL_ONE_PER_SM"),):
             if name in kv:
                 os.environ[env] = kv[name]
             else:
                 os.environ.pop(env, None)
-        if "carve" in kv:  # the carve-out is set when a forest is bound to the device: a forest of its own
-            os.environ["CCFD_GLOBAL_CARVEOUT"] = kv["carve"]
+        if "carve" in kv or "carves" in kv:  # carve-outs are set when a forest is bound to the device: a forest of its own
+            os.environ["CCFD_GLOBAL_CARVEOUT"] = kv.get("carve", "40")             # arrival-order kernel
+            os.environ["CCFD_GLOBAL_CARVEOUT_SORTED"] = kv.get("carves", "85")     # two-CTAs-per-SM kernel of sorted launches
             forest_v = model.Forest(fa)
         else:
-            os.environ.pop("CCFD_GLOBAL_CARVEOUT", None)
             forest_v = forest
         if "nt" in kv:
             os.environ["CCFD_GLOBAL_NT"] = kv["nt"]
