@@ -279,6 +279,19 @@ def run_latency_1k(forest, X, batches=10_000, rate_records_s=4e6, burst=64):
     res["replay"] = {"batches": len(a), **pct(a), "records_per_s_target": rate_records_s, "records_per_s_achieved": len(stream) / dt,
                      "burst_records": burst, "record_bytes": 120,
                      "path": "producer thread -> ccfd_batcher (pinned ring) -> CUDA graph per 1,024 records -> collector thread"}
+    # the same ring unpaced: how many 120-byte records per second it takes when the producer never waits
+    done = []
+    mb = ingest.MicroBatcher(sess, batch=1024, on_result=lambda first, p, l: done.append(len(p)))
+    t0 = time.perf_counter()
+    prod = threading.Thread(target=lambda: mb.replay(stream, records_per_s=0.0, burst=1024))
+    prod.start()
+    deadline = time.perf_counter() + 60.0
+    while sum(done) < len(stream) and time.perf_counter() < deadline:
+        mb.drain(50)
+    prod.join()
+    dt = time.perf_counter() - t0
+    mb.close()
+    res["replay_unpaced"] = {"records_per_s": len(stream) / dt, "batches": len(done), "burst_records": 1024}
     sess.close()
     return res
 
