@@ -263,6 +263,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    t_start, phases = time.perf_counter(), {}
+
+    def mark(name, _last=[time.perf_counter()]):
+        now = time.perf_counter()
+        phases[name] = round(now - _last[0], 2)
+        _last[0] = now
+
     if args.impl == "reference":
         return run_reference(args, rank, world)
     args.warmup = max(args.warmup, 3)
@@ -313,6 +320,7 @@ def main():
     fa = converter.ForestArrays.load(tmp)
     forest = model.Forest(fa, device=local_rank)
     info = forest.info
+    mark("imports_fit_upload")
 
     # ---- rows: this rank's contiguous range of the job
     n, total_rows = job_shape(args, world, rank)
@@ -324,6 +332,7 @@ def main():
     def step():
         forest.predict_proba_device(xs.data_ptr(), n, 30, out.data_ptr(), stream, args.kernel, sync=False)
 
+    mark("generate_rows")
     for _ in range(args.warmup):
         step()
     barrier()
@@ -364,6 +373,7 @@ def main():
                   "decisions_equal": bool(np.array_equal(got[:, 1] > 0.5, want[:, 1] > 0.5)), "max_abs_diff": float(np.abs(got - want).max()),
                   "against": f"scikit-learn {__import__('sklearn').__version__} predict_proba(n_jobs=1) on the same rows, this run"}
 
+    mark("timed_steps_and_parity")
     # ---- roofline of the dominant (only) kernel of a step
     peak, peak_src = FALLBACK_HBM_GBS, "fallback"
     try:
@@ -441,6 +451,7 @@ def main():
         del hx, hp, hd
     del xs, out
     torch.cuda.empty_cache()
+    mark("e2e")
 
     # ---- configs[4]: requests under bulk load, on every rank's GPU at the same time
     mixed = None
@@ -454,6 +465,7 @@ def main():
         else:
             mixed = {"n_gpus": 1, "clients_per_gpu": 5, **mine, "note": extra.MIXED_NOTE}
 
+    mark("mixed_load")
     latency = e2e_predict = config3 = cpu = None
     if rank == 0:
         # ---- configs[1]: 1,024-row micro-batches, closed loop and replayed at a fixed rate
@@ -461,13 +473,15 @@ def main():
             latency = extra.run_latency_1k(forest, X)
             # ---- the deployment's own e2e: the configs[0]-shaped batch through the Seldon class, pageable numpy
             e2e_predict = extra.run_e2e_predict(fa, X, device=local_rank)
+        mark("latency_and_e2e_predict")
         # ---- configs[2]: 500 unbounded trees x 10 M rows (one GPU)
         if world == 1 and not args.no_config3:
             config3 = extra.run_config3(args.config3_trees, 10_000_000, cpu_budget_s=0.0)
+        mark("config3")
         # ---- CPU baseline: scikit-learn on all host cores, bounded sample of the job's rows, N=1 only
         if world == 1 and not args.no_cpu_baseline:
             rows = host_sample(CPU_SAMPLE_ROWS)
-            best, calls = time_sklearn(rf, rows, budget_s=10.0, min_calls=2)
+            best, calls = time_sklearn(rf, rows, budget_s=6.0, min_calls=3)
             rf.n_jobs = 1  # the bit-exact order; also the faster CPU path for tiny requests (no joblib dispatch)
             t1 = time.perf_counter()
             rf.predict_proba(X)
@@ -486,6 +500,8 @@ def main():
             "config3": config3, "cpu_baseline": cpu, "clocks": clocks,
             "gpu_launches": args.steps, "wall_s_timed": wall, "checksum_p_fraud": checksum,
         }
+        mark("cpu_baseline")
+        line["phases_s"] = {**phases, "total": round(time.perf_counter() - t_start, 1)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
