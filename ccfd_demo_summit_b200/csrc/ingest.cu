@@ -53,9 +53,11 @@ class HostPool {
             std::unique_lock<std::mutex> lk(mu_);
             fn_ = &fn;
             n_parts_ = n_parts;
-            next_.store(0, std::memory_order_relaxed);
             pending_ = n_parts;
             err_ = nullptr;
+            // release: a worker still leaving the previous job's loop may pick a part of this one as soon as it
+            // sees the counter reset, and must then see this job's function and size too
+            next_.store(0, std::memory_order_release);
             ++generation_;
         }
         cv_work_.notify_all();
@@ -86,7 +88,7 @@ class HostPool {
     }
     void work_loop() {
         for (;;) {
-            const int i = next_.fetch_add(1, std::memory_order_relaxed);
+            const int i = next_.fetch_add(1, std::memory_order_acq_rel);
             if (i >= n_parts_) return;
             try {
                 (*fn_)(i);
