@@ -18,10 +18,14 @@
 //           16 consumer warps transpose their own rows and walk TPT trees x SPT rows per thread.
 //           Per-tree metadata and the top three levels of every tree are kernel parameters
 //           (constant bank).
+//           Forests small enough to sit in shared memory next to the rows take the forest-resident variant
+//           (RES): loaded once per CTA, the ring carries rows only, four trees x two rows per thread.
 //   SPLIT   latency.  Grid = row tiles x tree chunks so a 1-1024 row request still covers the
 //           chip; per-(tree,row) leaf values go to scratch and a second kernel adds them in tree
 //           order.
-//   GLOBAL  forests whose trees do not fit a shared-memory stage: nodes come from L1/L2/HBM.
+//   GLOBAL  forests whose trees do not fit a shared-memory stage: nodes come from L1/L2/HBM.  Bulk launches
+//           take their rows in the order of a counting sort on the forest's most used split features
+//           (sort.cu) and then hold two CTAs per SM (latency-bound once a warp's rows share their paths).
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
