@@ -35,7 +35,8 @@ __device__ __forceinline__ uint32_t key_bucket(const SortKey& sk, int k, float x
 // and each lane then picks its own row's key features from there.  Wide rows (pitch beyond the shared-memory
 // budget) fall back to strided loads.
 constexpr int kKeyWarps = 8;
-constexpr int kKeyMaxPitch = 65;
+constexpr int kKeyMaxPitch = 47;  // 8 warps x 32 rows x 47 floats = 48,128 bytes: within the 48 KB a kernel gets without opting in
+static_assert(kKeyWarps * 32 * kKeyMaxPitch * 4 <= 48 * 1024, "k_sort_keys' dynamic shared memory must fit the default limit");
 __global__ void __launch_bounds__(kKeyWarps * 32) k_sort_keys(const float* __restrict__ X, int64_t n, int64_t ld, int F, SortKey sk, int shift,
                                                               uint32_t* __restrict__ keys, uint32_t* __restrict__ hist) {
     extern __shared__ float rows_s[];

@@ -183,6 +183,17 @@ def test_row_presort_changes_no_bit(ccfd, monkeypatch):
         d, p = forest.decide(X32, 0.5, ge=True, want_proba=True, kernel="global")
         assert np.array_equal(d, P[:, 1] >= 0.5) and np.array_equal(bits(p), bits(P)), name
         forest.close()
+    # wide rows: the key kernel parks up to 46 features per row in shared memory and reads wider rows strided
+    # (found by scripts/stress_parity.py: 64 features used to overflow the default shared-memory limit)
+    import random_forests as rfs
+    from oracle import rf_oracle
+
+    for F in (46, 47, 64, 200):
+        raw = rfs.random_forest(100 + F, 9, 150, F, 0.3)
+        Xw = np.nan_to_num(rfs.random_rows(100 + F, raw, 3000), nan=0.25)
+        forest = model.Forest(_fa(raw))
+        assert np.array_equal(bits(_score_device(forest, Xw, "global")), bits(rf_oracle.predict_proba_c(raw, Xw))), F
+        forest.close()
 
 
 def test_fused_decision_matches_threshold_rule(ccfd):
