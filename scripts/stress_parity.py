@@ -54,5 +54,28 @@ for c in range(n_cfg):
             bad += 1
             print("MISMATCH", dict(seed=seed, n_trees=n_trees, max_internal=max_internal, F=F, skew=skew, n=n, kernel=k,
                                    rows_bad=int((got.view(np.uint64) != want[:m].view(np.uint64)).any(axis=1).sum())), flush=True)
+    # host paths: pageable float32 / float64 matrices (pipelined staging), and the one-call session request
+    host = []
+    if n >= 4097:
+        host.append(("host f32", lambda: forest.predict_proba(X)))
+        host.append(("rows f64", lambda: forest.predict_rows(X.astype(np.float64))))
+    elif forest.info["stream_kernel_ok"] or n <= 1024:
+        def via_session():
+            s = model.Session(forest, max(n, 32), 2)
+            try:
+                return s.score(int(rng.integers(2)), X.astype(np.float64) if rng.random() < 0.5 else X)
+            finally:
+                s.close()
+        host.append(("session", via_session))
+    for name, fn in host:
+        try:
+            got = fn()
+        except Exception as e:  # noqa: BLE001
+            bad += 1
+            print("ERROR", cfg, name, e, flush=True)
+            continue
+        if not np.array_equal(got.view(np.uint64), want.view(np.uint64)):
+            bad += 1
+            print("MISMATCH", cfg, name, flush=True)
     forest.close()
 print(f"{n_cfg} configurations, {bad} mismatches, {time.time() - t0:.0f} s")
