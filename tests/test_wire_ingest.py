@@ -430,3 +430,45 @@ def test_native_batcher_binary_records_replay_and_inf_refusal():
         ingest.MicroBatcher(model.Session(m.forest, max_batch=64, n_slots=1), batch=64)
     sess.close()
     m.close()
+
+
+@pytest.mark.gpu
+def test_http_server_with_coalescing_merges_concurrent_single_transaction_posts():
+    """CCFD_COALESCE / make_server(coalesce=True): single-transaction POSTs (the KIE server's pool of
+    clients, reference README.md:386-393, deploy/ccd-service.yaml:61-66) that arrive while a launch is in
+    flight share the next launch; every caller still gets its own row's probabilities, bit for bit."""
+    import urllib.request
+
+    _, m, X, P = _model()
+    srv = sh.make_server(m, port=0, coalesce=True)
+    port = srv.server_address[1]
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    results, errs = {}, []
+
+    def client(k):
+        try:
+            for i in range(25):
+                row = (k * 25 + i) % 600
+                body = json.dumps({"data": {"ndarray": [X[row].astype(np.float64).tolist()]}}).encode()
+                req = urllib.request.Request(f"http://127.0.0.1:{port}/predict", data=body, headers={"Content-Type": "application/json"})
+                msg = json.loads(urllib.request.urlopen(req, timeout=30).read())
+                results[(k, i)] = (row, np.asarray(msg["data"]["ndarray"], dtype=np.float64))
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    try:
+        th = [threading.Thread(target=client, args=(k,)) for k in range(16)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join(timeout=120)
+        assert not errs, errs[:1]
+        assert len(results) == 400
+        for row, got in results.values():
+            assert got.shape == (1, 2) and np.array_equal(bits(got), bits(P[row:row + 1]))
+        co = srv.app.coalescer
+        assert co is not None and co.rows_scored == 400 and co.launches <= 400
+    finally:
+        srv.shutdown()
+        srv.app.close()
+        m.close()
